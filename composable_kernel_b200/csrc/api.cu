@@ -1,0 +1,264 @@
+// api.cu -- the C ABI of libckb.so (include/ckb.h): argument validation (CK's IsSupportedArgument),
+// kernel selection (CK's instance choice), workspace sizing, launch.  No CPU fallback exists here.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace ckb {
+namespace {
+
+bool is_f16ish(int dt) { return dt == CKB_F16 || dt == CKB_BF16; }
+
+int unsupported(ckb_gemm_plan* plan, const char* fmt, ...)
+{
+    char buf[256];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    last_error()    = buf;
+    plan->supported = 0;
+    plan->kernel_id = KID_NONE;
+    return CKB_OK;
+}
+
+uint64_t d_bytes(const ckb_gemm_problem& p, int i)
+{
+    const uint64_t e = dtype_bytes(p.d_dtype[i]);
+    const uint64_t m = p.d_sm[i] ? p.M : 1, n = p.d_sn[i] ? p.N : 1;
+    return e * m * n;
+}
+
+uint64_t algo_bytes(const ckb_gemm_problem& p)
+{
+    uint64_t b = uint64_t(p.M) * p.K * dtype_bytes(p.a_dtype);
+    if(p.b_dtype == CKB_I4) b += uint64_t(p.N) * p.K / 2;
+    else b += uint64_t(p.N) * p.K * dtype_bytes(p.b_dtype);
+    if(p.b_op == CKB_BOP_GROUP)
+    {
+        const uint64_t g = (p.K + p.group_size - 1) / p.group_size;
+        b += g * p.N * dtype_bytes(p.s_dtype);
+        if(p.zero) b += g * p.N;
+    }
+    else if(p.b_op == CKB_BOP_MULTIPLY || p.b_op == CKB_BOP_FPAINTB)
+        b += uint64_t(p.N) * dtype_bytes(p.s_dtype);
+    for(int i = 0; i < p.num_d; ++i) b += d_bytes(p, i);
+    b += uint64_t(p.M) * p.N * dtype_bytes(p.e_dtype);
+    return b;
+}
+
+int needed_d(int cde)
+{
+    static const int need[] = {0, 1, 0, 1, 1, 2, 1, 2, 2, 0, 1, 1, 2};
+    return (cde >= 0 && cde <= CKB_CDE_ADD_ACT_MUL2_CLAMP) ? need[cde] : 99;
+}
+
+} // namespace
+} // namespace ckb
+
+using namespace ckb;
+
+extern "C" {
+
+const char* ckb_last_error(void) { return last_error().c_str(); }
+int ckb_version(void) { return CKB_VERSION; }
+int ckb_device_sm_count(void) { return device_info().ok ? device_info().sm_count : -1; }
+
+int ckb_gemm_query(const ckb_gemm_problem* pp, ckb_gemm_plan* plan)
+{
+    if(!pp || !plan) return set_error(CKB_ERR_INVALID, "null problem/plan");
+    const ckb_gemm_problem& p = *pp;
+    memset(plan, 0, sizeof *plan);
+    if(p.M < 0 || p.N < 0 || p.K < 0) return set_error(CKB_ERR_INVALID, "negative GEMM size");
+    plan->flops      = 2ull * p.M * p.N * p.K;
+    plan->algo_bytes = algo_bytes(p);
+    if(p.K <= 0) return unsupported(plan, "K must be positive");
+    if(p.num_d < needed_d(p.cde_op) || p.num_d > CKB_MAX_D)
+        return unsupported(plan, "cde_op %d needs %d D tensors, got %d", p.cde_op, needed_d(p.cde_op), p.num_d);
+    if(p.a_layout != CKB_ROW) return unsupported(plan, "A must be row-major (mk_*)");
+    for(int i = 0; i < needed_d(p.cde_op); ++i)
+        if(!p.d[i]) return unsupported(plan, "D%d pointer is null", i);
+    if(p.M == 0 || p.N == 0)
+    {
+        plan->supported = 1; // nothing to compute (empty problem): run() is a no-op
+        plan->kernel_id = KID_NONE;
+        snprintf(plan->kernel_name, sizeof plan->kernel_name, "empty");
+        return CKB_OK;
+    }
+    if(!p.a || !p.b || !p.e) return unsupported(plan, "A/B/E pointer is null");
+
+    if(p.a_dtype == CKB_I8 || (is_f16ish(p.a_dtype) && p.b_dtype == p.a_dtype))
+    {
+        // ---- K3: SS GEMM ----
+        if(p.b_dtype != p.a_dtype) return unsupported(plan, "int8 A needs int8 B");
+        if(p.b_layout != CKB_COL) return unsupported(plan, "SS kernel needs K-major (column-major) B");
+        if(p.b_op != CKB_BOP_PASSTHROUGH) return unsupported(plan, "SS kernel supports PassThrough B only");
+        const bool i8 = p.a_dtype == CKB_I8;
+        if(i8)
+        {
+            switch(p.cde_op)
+            {
+            case CKB_CDE_PASSTHROUGH: case CKB_CDE_ACT_MUL_CLAMP: case CKB_CDE_ADD_ACT_MUL_CLAMP:
+            case CKB_CDE_ACT_MUL2_CLAMP: case CKB_CDE_ADD_ACT_MUL2_CLAMP: case CKB_CDE_MULTIPLY_MULTIPLY: break;
+            default: return unsupported(plan, "cde_op %d is not defined on int32 accumulators", p.cde_op);
+            }
+            if((p.cde_op == CKB_CDE_ADD_ACT_MUL_CLAMP || p.cde_op == CKB_CDE_ADD_ACT_MUL2_CLAMP) && p.d_dtype[0] != CKB_I32)
+                return unsupported(plan, "bias must be int32");
+        }
+        else if(p.cde_op > CKB_CDE_MULTIPLY_MULTIPLY)
+            return unsupported(plan, "quantization epilogues need int8 inputs");
+        const int eb = dtype_bytes(p.a_dtype);
+        if((p.lda * eb) % 16 || (p.ldb * eb) % 16) return unsupported(plan, "lda/ldb must be 16-byte multiples (K %% %d)", 16 / eb);
+        if(p.lda < p.K || p.ldb < p.K || p.lde < p.N) return unsupported(plan, "leading dimension smaller than extent");
+        if(!device_info().ok) { plan->supported = 0; return set_error(CKB_ERR_NO_DEVICE, "no sm_100 device"); }
+        if(int rc = plan_gemm_ss(p, *plan)) { if(rc == CKB_ERR_UNSUPPORTED) { plan->supported = 0; return CKB_OK; } return rc; }
+        plan->kernel_id = KID_GEMM_SS;
+        plan->supported = 1;
+        return CKB_OK;
+    }
+
+    if(!is_f16ish(p.a_dtype)) return unsupported(plan, "A must be fp16, bf16 or int8");
+    // ---- K1/K2: weight-quantized GEMM ----
+    if(p.cde_op > CKB_CDE_MULTIPLY_MULTIPLY) return unsupported(plan, "quantization epilogues need int8 inputs");
+    if(p.e_dtype != CKB_F16 && p.e_dtype != CKB_BF16 && p.e_dtype != CKB_F32) return unsupported(plan, "E must be f16/bf16/f32");
+    switch(p.b_op)
+    {
+    case CKB_BOP_GROUP:
+        if(p.b_dtype != CKB_I4 || p.b_layout != CKB_PREPACKED) return unsupported(plan, "GROUP dequant needs pre-packed int4 B (ckb_prepack_b_int4)");
+        if(p.group_size != 128) return unsupported(plan, "group_size must be 128");
+        if(!p.scale || p.s_dtype != p.a_dtype) return unsupported(plan, "group scales must have A's type");
+        if(p.N % 8 || (p.zero && p.N % 16)) return unsupported(plan, "N must be a multiple of 8 (16 with zero points)");
+        if(p.zero_const < 0 || p.zero_const > 15) return unsupported(plan, "zero_const out of range");
+        break;
+    case CKB_BOP_MULTIPLY:
+        if(p.a_dtype != CKB_BF16 || p.b_dtype != CKB_I8 || p.s_dtype != CKB_BF16 || !p.scale)
+            return unsupported(plan, "Multiply B-op: bf16 A, int8 B0, bf16 B1");
+        break;
+    case CKB_BOP_FPAINTB:
+        if(p.a_dtype != CKB_F16 || p.b_dtype != CKB_U8 || p.s_dtype != CKB_F16 || !p.scale)
+            return unsupported(plan, "fpAintB: fp16 A, biased uint8 B (ckb_prepack_b_u8), fp16 scale");
+        break;
+    case CKB_BOP_PASSTHROUGH:
+        if(p.b_dtype != CKB_I8) return unsupported(plan, "PassThrough B-op needs int8 B");
+        break;
+    default: return unsupported(plan, "unknown b_op %d", p.b_op);
+    }
+    if(p.b_op != CKB_BOP_GROUP)
+    {
+        if(p.b_layout != CKB_COL) return unsupported(plan, "int8 B must be K-major (column-major: mk_nk_mn)");
+        if(p.ldb % 16 || p.ldb < p.K) return unsupported(plan, "ldb must be a multiple of 16 and >= K");
+    }
+    if(p.lda % 8 || p.lda < p.K) return unsupported(plan, "lda must be a multiple of 8 and >= K");
+    if(p.lde < p.N) return unsupported(plan, "lde < N");
+    if(!device_info().ok) { plan->supported = 0; return set_error(CKB_ERR_NO_DEVICE, "no sm_100 device"); }
+    {
+        // M <= 64: one pass of the decode kernel.  Larger M: the same kernel over 64-row slabs
+        // (interim; the persistent-tile prefill kernel replaces this for M > 64).
+        ckb_gemm_problem q = p;
+        q.M = std::min(p.M, 64);
+        if(int rc = plan_wq_decode(q, *plan)) { if(rc == CKB_ERR_UNSUPPORTED) { plan->supported = 0; return CKB_OK; } return rc; }
+        plan->kernel_id = KID_WQ_DECODE;
+        plan->supported = 1;
+    }
+    return CKB_OK;
+}
+
+int ckb_gemm_run(const ckb_gemm_problem* pp, const ckb_gemm_plan* plan, void* workspace, void* stream)
+{
+    if(!pp || !plan) return set_error(CKB_ERR_INVALID, "null problem/plan");
+    if(!plan->supported) return set_error(CKB_ERR_UNSUPPORTED, "plan is not supported: %s", last_error().c_str());
+    if(pp->M == 0 || pp->N == 0) return CKB_OK;
+    if(!device_info().ok) return set_error(CKB_ERR_NO_DEVICE, "no sm_100 device");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    switch(plan->kernel_id)
+    {
+    case KID_GEMM_SS: return run_gemm_ss(*pp, *plan, st);
+    case KID_WQ_DECODE: {
+        if(pp->M <= 64) return run_wq_decode(*pp, *plan, workspace, st);
+        // slabs of 64 rows; each slab needs its own activation tensor map
+        for(int m0 = 0; m0 < pp->M; m0 += 64)
+        {
+            ckb_gemm_problem q = *pp;
+            q.M = std::min(64, pp->M - m0);
+            q.a = static_cast<const uint8_t*>(pp->a) + size_t(m0) * pp->lda * 2;
+            q.e = static_cast<uint8_t*>(pp->e) + size_t(m0) * pp->lde * dtype_bytes(pp->e_dtype);
+            for(int i = 0; i < pp->num_d; ++i)
+                q.d[i] = static_cast<const uint8_t*>(pp->d[i]) + size_t(m0) * pp->d_sm[i] * dtype_bytes(pp->d_dtype[i]);
+            ckb_gemm_plan sub;
+            memset(&sub, 0, sizeof sub);
+            if(int rc = plan_wq_decode(q, sub)) return rc;
+            sub.supported = 1;
+            if(int rc = run_wq_decode(q, sub, workspace, st)) return rc;
+        }
+        return CKB_OK;
+    }
+    default: return set_error(CKB_ERR_INVALID, "bad kernel id %d", plan->kernel_id);
+    }
+}
+
+uint64_t ckb_gemm_host_staging_bytes(const ckb_gemm_problem* p)
+{
+    if(!p) return 0;
+    auto al = [](uint64_t v) { return (v + 255) & ~uint64_t(255); };
+    uint64_t b = al(uint64_t(p->M) * p->lda * dtype_bytes(p->a_dtype));
+    for(int i = 0; i < p->num_d; ++i)
+        b += al((uint64_t(p->M - 1) * p->d_sm[i] + uint64_t(p->N - 1) * p->d_sn[i] + 1) * dtype_bytes(p->d_dtype[i]));
+    b += al(uint64_t(p->M) * p->lde * dtype_bytes(p->e_dtype));
+    return b;
+}
+
+int ckb_gemm_run_host(const ckb_gemm_problem* pp, void* staging, void* workspace, void* stream)
+{
+    if(!pp || !staging) return set_error(CKB_ERR_INVALID, "null problem/staging");
+    if(pp->M == 0 || pp->N == 0) return CKB_OK;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    auto al = [](uint64_t v) { return (v + 255) & ~uint64_t(255); };
+    ckb_gemm_problem q = *pp;
+    uint8_t* cur = static_cast<uint8_t*>(staging);
+    const uint64_t a_bytes = (uint64_t(pp->M - 1) * pp->lda + pp->K) * dtype_bytes(pp->a_dtype);
+    CKB_CUDA_CHECK(cudaMemcpyAsync(cur, pp->a, a_bytes, cudaMemcpyHostToDevice, st));
+    q.a = cur;
+    cur += al(uint64_t(pp->M) * pp->lda * dtype_bytes(pp->a_dtype));
+    for(int i = 0; i < pp->num_d; ++i)
+    {
+        const uint64_t bytes = (uint64_t(pp->M - 1) * pp->d_sm[i] + uint64_t(pp->N - 1) * pp->d_sn[i] + 1) * dtype_bytes(pp->d_dtype[i]);
+        CKB_CUDA_CHECK(cudaMemcpyAsync(cur, pp->d[i], bytes, cudaMemcpyHostToDevice, st));
+        q.d[i] = cur;
+        cur += al(bytes);
+    }
+    q.e = cur;
+    ckb_gemm_plan plan;
+    if(int rc = ckb_gemm_query(&q, &plan)) return rc;
+    if(!plan.supported) return set_error(CKB_ERR_UNSUPPORTED, "%s", last_error().c_str());
+    if(int rc = ckb_gemm_run(&q, &plan, workspace, stream)) return rc;
+    const uint64_t e_bytes = (uint64_t(pp->M - 1) * pp->lde + pp->N) * dtype_bytes(pp->e_dtype);
+    CKB_CUDA_CHECK(cudaMemcpyAsync(pp->e, cur, e_bytes, cudaMemcpyDeviceToHost, st));
+    CKB_CUDA_CHECK(cudaStreamSynchronize(st));
+    return CKB_OK;
+}
+
+int ckb_prepack_b_u8(const void* src, void* dst, int64_t n, void* stream)
+{
+    if(!src || !dst || n < 0) return set_error(CKB_ERR_INVALID, "bad prepack arguments");
+    if(!device_info().ok) return set_error(CKB_ERR_NO_DEVICE, "no sm_100 device");
+    return launch_prepack_u8(src, dst, n, static_cast<cudaStream_t>(stream));
+}
+
+uint64_t ckb_prepack_b_int4_bytes(int32_t N, int32_t K)
+{
+    if(N <= 0 || K <= 0) return 0;
+    return uint64_t((N + 127) / 128) * ((K + 127) / 128) * 8192;
+}
+
+int ckb_prepack_b_int4(const void* src, int64_t sk, int64_t sn, int32_t N, int32_t K, void* dst, void* stream)
+{
+    if(!src || !dst || N < 0 || K < 0) return set_error(CKB_ERR_INVALID, "bad prepack arguments");
+    if(!device_info().ok) return set_error(CKB_ERR_NO_DEVICE, "no sm_100 device");
+    return launch_prepack_int4(src, sk, sn, N, K, dst, static_cast<cudaStream_t>(stream));
+}
+
+int ckb_grouped_gemm_run(const ckb_gemm_problem*, const ckb_group_arg*, int32_t, int32_t, void*)
+{
+    return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM not built yet");
+}
+
+} // extern "C"

@@ -1,0 +1,96 @@
+// common.cu -- error state, device probing, TMA descriptor encoding.
+#include "common.cuh"
+
+#include <mutex>
+
+namespace ckb {
+
+std::string& last_error()
+{
+    static thread_local std::string s;
+    return s;
+}
+
+int set_error(int code, const char* fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    last_error() = buf;
+    return code;
+}
+
+const DeviceInfo& device_info()
+{
+    static DeviceInfo info;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        int n = 0;
+        if(cudaGetDeviceCount(&n) != cudaSuccess || n == 0)
+        {
+            cudaGetLastError();
+            return;
+        }
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceProp p{};
+        if(cudaGetDeviceProperties(&p, dev) != cudaSuccess) return;
+        info.sm_count = p.multiProcessorCount;
+        info.cc_major = p.major;
+        info.cc_minor = p.minor;
+        cudaDeviceGetAttribute(&info.max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+        info.ok = (p.major == 10);
+    });
+    return info;
+}
+
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn()
+{
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) ==
+               cudaSuccess &&
+           qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+        else
+            cudaGetLastError();
+    });
+    return fn;
+}
+
+int encode_tmap_2d(CUtensorMap* out, CUtensorMapDataType dt, int elem_bytes, const void* base,
+                   uint64_t rows, uint64_t cols, uint64_t ld_elems, uint32_t box_rows,
+                   uint32_t box_cols, CUtensorMapSwizzle swz)
+{
+    EncodeTiledFn fn = get_encode_fn();
+    if(!fn) return set_error(CKB_ERR_NO_DEVICE, "cuTensorMapEncodeTiled entry point unavailable");
+    if((reinterpret_cast<uintptr_t>(base) & 15) != 0)
+        return set_error(CKB_ERR_UNSUPPORTED, "TMA base pointer must be 16-byte aligned");
+    if((ld_elems * elem_bytes) % 16 != 0)
+        return set_error(CKB_ERR_UNSUPPORTED, "TMA row pitch must be a multiple of 16 bytes");
+    cuuint64_t gdim[2]    = {cols, rows};
+    cuuint64_t gstride[1] = {ld_elems * uint64_t(elem_bytes)};
+    cuuint32_t box[2]     = {box_cols, box_rows};
+    cuuint32_t estr[2]    = {1, 1};
+    CUresult r = fn(out, dt, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if(r != CUDA_SUCCESS)
+        return set_error(CKB_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d "
+                         "(rows %llu cols %llu ld %llu box %ux%u)", int(r),
+                         (unsigned long long)rows, (unsigned long long)cols,
+                         (unsigned long long)ld_elems, box_rows, box_cols);
+    return CKB_OK;
+}
+
+} // namespace ckb

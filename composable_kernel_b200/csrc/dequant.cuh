@@ -1,0 +1,121 @@
+// dequant.cuh -- in-register weight unpack/dequant for the TMEM-A GEMM kernels (K1/K2).
+// The role of CK's ThreadwiseTensorSliceTransfer_v3r1_dequant + FastNumericArrayConverter<uint8_t,half_t,N>
+// (thread/threadwise_tensor_slice_transfer_v3r1_dequant.hpp:429-549,
+//  element/unary_element_wise_operation.hpp:1056-1122) and of the Multiply B-functor inside
+// ThreadwiseTensorSliceTransfer_v7r2 (binary_element_wise_operation.hpp:184-190), done with
+// prmt / lop3 magic numbers.  Every routine produces 16-bit pairs packed (k even -> low half) in
+// the order the tcgen05 TMEM A operand wants: one 32-bit column = two consecutive k.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
+#include <cstdint>
+
+namespace ckb {
+
+enum WFmt : int {
+    WF_W4_GROUP   = 0, // pre-packed 4-bit codes, (q - zp) exact in A's type, group scale applied to fp32 partial sums
+    WF_W8_MUL     = 1, // int8 (signed) * bf16 scale[n] -> bf16 by truncation (Multiply<bhalf_t,int8_t,bhalf_t>)
+    WF_W8_FPAINTB = 2, // biased uint8 -> fp16(u8 - 128) * fp16 scale[n], one fp16 rounding (fpAintB)
+    WF_W8_PASS    = 3  // int8 (signed) -> A's type exactly (PassThrough)
+};
+
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel)
+{
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
+    return r;
+}
+template <int LUT>
+__device__ __forceinline__ uint32_t lop3(uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t r;
+    asm("lop3.b32 %0, %1, %2, %3, %4;" : "=r"(r) : "r"(a), "r"(b), "r"(c), "n"(LUT));
+    return r;
+}
+__device__ __forceinline__ uint32_t hsub2_f16(uint32_t a, uint32_t b)
+{
+    uint32_t r;
+    asm("sub.rn.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+}
+__device__ __forceinline__ uint32_t hmul2_f16(uint32_t a, uint32_t b)
+{
+    uint32_t r;
+    asm("mul.rn.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+}
+__device__ __forceinline__ uint32_t hsub2_bf16(uint32_t a, uint32_t b)
+{
+    uint32_t r;
+    asm("sub.rn.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+}
+
+// ---- W4: one 32-bit word = 8 codes stored in the interleaved order [k0,k2,k4,k6,k1,k3,k5,k7]
+// (nibble 0 = bits 0..3).  (w >> 4i) & 0x000F000F puts (k_2i, k_2i+1) in the two halves.
+//   bf16: 0x4300 | q = 128 + q exactly;  fp16: 0x6400 | q = 1024 + q exactly
+// `zmagic` = packed (magic + zero_point) in A's type; the subtraction is exact.
+template <bool F16>
+__device__ __forceinline__ void dequant_w4_word(uint32_t w, uint32_t zmagic, uint32_t* out4)
+{
+    constexpr uint32_t MAGIC = F16 ? 0x64006400u : 0x43004300u;
+#pragma unroll
+    for(int i = 0; i < 4; ++i)
+    {
+        // (x & 0x000F000F) | MAGIC   -> lop3 LUT (a & b) | c = 0xEA
+        const uint32_t t = lop3<0xEA>(w >> (4 * i), 0x000F000Fu, MAGIC);
+        out4[i]          = F16 ? hsub2_f16(t, zmagic) : hsub2_bf16(t, zmagic);
+    }
+}
+
+// ---- W8 fpAintB (fp16): u8 -> 0x6400|u8 = 1024 + u8; minus 1152 (= 0x6480) removes the +128 bias
+// (the reference's own trick, unary_element_wise_operation.hpp:1061-1091); times scale: ONE rounding.
+__device__ __forceinline__ void dequant_u8x4_fpaintb(uint32_t w, uint32_t scale2, uint32_t* out2)
+{
+    const uint32_t lo = prmt(w, 0x64646464u, 0x4140); // bytes: [b0, 0x64, b1, 0x64]
+    const uint32_t hi = prmt(w, 0x64646464u, 0x4342); // bytes: [b2, 0x64, b3, 0x64]
+    out2[0]           = hmul2_f16(hsub2_f16(lo, 0x64806480u), scale2);
+    out2[1]           = hmul2_f16(hsub2_f16(hi, 0x64806480u), scale2);
+}
+
+// ---- W8 signed int8 -> exact value in fp32: flip the sign bit (int8 + 128 as u8), place the byte in
+// the mantissa of 2^23 (0x4B000000), subtract 2^23 + 128.
+__device__ __forceinline__ float s8_byte_to_f32(uint32_t w_biased, int byte)
+{
+    const uint32_t sel = 0x7650u | uint32_t(byte); // [byte, 0x00, 0x00, 0x4B] of (w, 0x4B000000)
+    return __uint_as_float(prmt(w_biased, 0x4B000000u, sel)) - 8388736.0f;
+}
+
+// Multiply<bhalf_t,int8_t,bhalf_t>: truncate(float(q) * float(s)) -- q*s is exact in fp32 (8 x 8 bits)
+__device__ __forceinline__ void dequant_s8x4_mul_bf16(uint32_t w, float scale, uint32_t* out2)
+{
+    const uint32_t wb = w ^ 0x80808080u;
+    const float f0 = s8_byte_to_f32(wb, 0) * scale, f1 = s8_byte_to_f32(wb, 1) * scale;
+    const float f2 = s8_byte_to_f32(wb, 2) * scale, f3 = s8_byte_to_f32(wb, 3) * scale;
+    out2[0] = prmt(__float_as_uint(f0), __float_as_uint(f1), 0x7632); // high halves: truncation
+    out2[1] = prmt(__float_as_uint(f2), __float_as_uint(f3), 0x7632);
+}
+
+// PassThrough<AType,int8_t>: exact (|q| <= 128 fits both 16-bit types)
+template <bool F16>
+__device__ __forceinline__ void dequant_s8x4_pass(uint32_t w, uint32_t* out2)
+{
+    const uint32_t wb = w ^ 0x80808080u;
+    if(F16)
+    {
+        const uint32_t lo = prmt(wb, 0x64646464u, 0x4140);
+        const uint32_t hi = prmt(wb, 0x64646464u, 0x4342);
+        out2[0]           = hsub2_f16(lo, 0x64806480u);
+        out2[1]           = hsub2_f16(hi, 0x64806480u);
+    }
+    else
+    {
+        const float f0 = s8_byte_to_f32(wb, 0), f1 = s8_byte_to_f32(wb, 1);
+        const float f2 = s8_byte_to_f32(wb, 2), f3 = s8_byte_to_f32(wb, 3);
+        out2[0] = prmt(__float_as_uint(f0), __float_as_uint(f1), 0x7632);
+        out2[1] = prmt(__float_as_uint(f2), __float_as_uint(f3), 0x7632);
+    }
+}
+
+} // namespace ckb

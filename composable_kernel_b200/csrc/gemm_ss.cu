@@ -1,0 +1,341 @@
+// gemm_ss.cu -- K3: both operands streamed by TMA into a 128B-swizzled smem ring and consumed by
+// tcgen05.mma straight from shared memory (SS form).  kind::i8 (s8 x s8 -> s32 in TMEM) serves
+// CK's int8 quantized GEMM (example/14_gemm_quantization, DeviceGemmMultipleD_Xdl_CShuffle) and
+// the int8 MultiplyMultiply composition; kind::f16 (bf16/fp16 -> fp32) is the dense comparator.
+//
+// Replaces: kernel_gemm_multiple_d_xdl_cshuffle (grid/gridwise_gemm_multiple_d_xdl_cshuffle.hpp:77,499)
+//           and the multi-D flavour of kernel_gemm_xdl_cshuffle_v3 (grid/gridwise_gemm_xdl_cshuffle_v3_multi_d.hpp).
+//
+// CTA = 8 warps, persistent over output tiles of 128 (M) x 256 (N):
+//   warp 0    TMA producer          (empty[s] -> full[s])
+//   warp 1    tcgen05.mma issuer    (full[s] -> empty[s]; tmem_empty[a] -> tmem_full[a])
+//   warp 2    TMEM allocator
+//   warp 4-7  epilogue              (tmem_full[a] -> tmem_empty[a]); warp w owns TMEM lanes 32*(w%4)..
+// TMEM: two 256-column fp32/s32 accumulators (all 512 columns) so the epilogue of tile i overlaps
+// the main loop of tile i+1.
+#include "common.cuh"
+#include "epilogue.cuh"
+#include "kernels.h"
+#include "ptx.cuh"
+
+namespace ckb {
+
+namespace {
+
+constexpr int SS_BM       = 128;
+constexpr int SS_BN       = 256;
+constexpr int SS_BK_BYTES = 128; // one swizzle atom of K per stage row
+constexpr int SS_STAGES   = 4;
+constexpr int SS_A_BYTES  = SS_BM * SS_BK_BYTES;
+constexpr int SS_B_BYTES  = SS_BN * SS_BK_BYTES;
+constexpr int SS_STAGE_BYTES = SS_A_BYTES + SS_B_BYTES;
+constexpr int SS_THREADS  = 256;
+constexpr int SS_SMEM     = SS_STAGES * SS_STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+
+struct SSArgs
+{
+    int M, N;
+    int num_kb;     // K blocks of 128 bytes
+    int kb_elems;   // elements per K block (128 for i8, 64 for 16-bit)
+    int num_m_blk, num_n_blk;
+    uint32_t idesc;
+    int is_i8;
+    EpiParams ep;
+};
+
+__device__ __forceinline__ void tile_coord(int t, int num_m_blk, int num_n_blk, int& mb, int& nb)
+{
+    // bands of 8 M-blocks; inside a band N-major so concurrently running CTAs share B panels and
+    // a band of A stays L2 resident (the role of CK's BlockToCTileMap_Grouped_M00_N0_M01Adapt,
+    // grid/block_to_ctile_map.hpp:266-390).
+    constexpr int GROUP = 8;
+    const int per_band  = GROUP * num_n_blk;
+    const int band      = t / per_band;
+    const int first_m   = band * GROUP;
+    const int rows      = min(GROUP, num_m_blk - first_m);
+    const int r         = t - band * per_band;
+    mb                  = first_m + r % rows;
+    nb                  = r / rows;
+}
+
+__device__ __forceinline__ void
+ss_epilogue_chunk(const SSArgs& a, int m, int n0, const uint32_t* r)
+{
+    const EpiParams& ep = a.ep;
+    if(m >= ep.M || n0 >= ep.N) return;
+    if(a.is_i8)
+    {
+        if(ep.cde_op == CKB_CDE_PASSTHROUGH && (ep.e_dtype == CKB_I32 || ep.e_dtype == CKB_I8))
+        {
+            const long long base = (long long)m * ep.lde + n0;
+            if(ep.e_dtype == CKB_I32)
+            {
+                int32_t* e = static_cast<int32_t*>(ep.e) + base;
+                if(n0 + 32 <= ep.N && ((reinterpret_cast<uintptr_t>(e) & 15) == 0))
+                {
+#pragma unroll
+                    for(int i = 0; i < 32; i += 4)
+                        *reinterpret_cast<uint4*>(e + i) = make_uint4(r[i], r[i + 1], r[i + 2], r[i + 3]);
+                }
+                else
+                {
+#pragma unroll
+                    for(int i = 0; i < 32; ++i)
+                        if(n0 + i < ep.N) e[i] = int32_t(r[i]);
+                }
+            }
+            else
+            {
+                int8_t* e = static_cast<int8_t*>(ep.e) + base;
+#pragma unroll
+                for(int i = 0; i < 32; ++i)
+                    if(n0 + i < ep.N) e[i] = static_cast<int8_t>(int32_t(r[i]));
+            }
+            return;
+        }
+        float v[32];
+#pragma unroll
+        for(int i = 0; i < 32; ++i)
+        {
+            const int n = n0 + i;
+            const void* dptr[CKB_MAX_D] = {ep.d[0], ep.d[1]};
+            long long doff[CKB_MAX_D];
+            doff[0] = (long long)m * ep.d_sm[0] + (long long)n * ep.d_sn[0];
+            doff[1] = (long long)m * ep.d_sm[1] + (long long)n * ep.d_sn[1];
+            v[i]    = (n < ep.N) ? cde_apply_i32(ep, int32_t(r[i]), dptr, doff) : 0.f;
+        }
+        store_row_f32<32>(ep, m, n0, v);
+    }
+    else
+    {
+        float v[32];
+#pragma unroll
+        for(int i = 0; i < 32; ++i)
+        {
+            const int n = n0 + i;
+            float d0 = 0.f, d1 = 0.f;
+            if(n < ep.N)
+            {
+                if(ep.num_d > 0) d0 = load_d_f32(ep.d_dtype[0], ep.d[0], (long long)m * ep.d_sm[0] + (long long)n * ep.d_sn[0]);
+                if(ep.num_d > 1) d1 = load_d_f32(ep.d_dtype[1], ep.d[1], (long long)m * ep.d_sm[1] + (long long)n * ep.d_sn[1]);
+            }
+            v[i] = cde_apply_f32(ep, __uint_as_float(r[i]), d0, d1);
+        }
+        store_row_f32<32>(ep, m, n0, v);
+    }
+}
+
+__global__ void __launch_bounds__(SS_THREADS, 1)
+gemm_ss_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               const SSArgs args)
+{
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bar_base  = smem_base + SS_STAGES * SS_STAGE_BYTES;
+    auto full_bar   = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar  = [&](int s) { return bar_base + 8u * (SS_STAGES + s); };
+    auto tfull_bar  = [&](int a) { return bar_base + 8u * (2 * SS_STAGES + a); };
+    auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * SS_STAGES + 2 + a); };
+    const uint32_t tmem_slot = bar_base + 8u * (2 * SS_STAGES + 4);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if(warp == 0 && lane == 0)
+    {
+        ptx::prefetch_tmap(&tmA);
+        ptx::prefetch_tmap(&tmB);
+    }
+    if(warp == 1 && lane == 0)
+    {
+        for(int s = 0; s < SS_STAGES; ++s)
+        {
+            ptx::mbar_init(full_bar(s), 1);
+            ptx::mbar_init(empty_bar(s), 1);
+        }
+        for(int a = 0; a < 2; ++a)
+        {
+            ptx::mbar_init(tfull_bar(a), 1);
+            ptx::mbar_init(tempty_bar(a), 4);
+        }
+        ptx::fence_mbar_init();
+    }
+    if(warp == 2)
+    {
+        ptx::tmem_alloc<512>(tmem_slot);
+        ptx::tmem_relinquish();
+    }
+    ptx::tcgen05_fence_before_sync();
+    __syncthreads();
+    ptx::tcgen05_fence_after_sync();
+    uint32_t tmem_base;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+    const int num_tiles = args.num_m_blk * args.num_n_blk;
+    const int num_kb    = args.num_kb;
+
+    if(warp == 0)
+    {
+        // ===================== TMA producer =====================
+        if(lane == 0)
+        {
+            int s = 0;
+            uint32_t ph = 0;
+            for(int t = blockIdx.x; t < num_tiles; t += gridDim.x)
+            {
+                int mb, nb;
+                tile_coord(t, args.num_m_blk, args.num_n_blk, mb, nb);
+                for(int kb = 0; kb < num_kb; ++kb)
+                {
+                    ptx::mbar_wait(empty_bar(s), ph ^ 1);
+                    ptx::mbar_arrive_expect_tx(full_bar(s), SS_STAGE_BYTES);
+                    const uint32_t sa = smem_base + s * SS_STAGE_BYTES;
+                    ptx::tma_load_2d(sa, &tmA, full_bar(s), kb * args.kb_elems, mb * SS_BM);
+                    ptx::tma_load_2d(sa + SS_A_BYTES, &tmB, full_bar(s), kb * args.kb_elems, nb * SS_BN);
+                    if(++s == SS_STAGES) { s = 0; ph ^= 1; }
+                }
+            }
+        }
+    }
+    else if(warp == 1)
+    {
+        // ===================== MMA issuer =====================
+        int s = 0;
+        uint32_t ph = 0;
+        int as = 0;
+        uint32_t aph = 0;
+        for(int t = blockIdx.x; t < num_tiles; t += gridDim.x)
+        {
+            ptx::mbar_wait(tempty_bar(as), aph ^ 1);
+            ptx::tcgen05_fence_after_sync();
+            const uint32_t d_tmem = tmem_base + as * SS_BN;
+            for(int kb = 0; kb < num_kb; ++kb)
+            {
+                ptx::mbar_wait(full_bar(s), ph);
+                ptx::tcgen05_fence_after_sync();
+                if(lane == 0)
+                {
+                    const uint32_t sa = smem_base + s * SS_STAGE_BYTES;
+                    const uint64_t da = ptx::make_smem_desc_sw128(sa, 1024);
+                    const uint64_t db = ptx::make_smem_desc_sw128(sa + SS_A_BYTES, 1024);
+#pragma unroll
+                    for(int j = 0; j < SS_BK_BYTES / 32; ++j)
+                    {
+                        // +32 bytes of K inside the swizzle atom = +2 in the (addr >> 4) field
+                        if(args.is_i8)
+                            ptx::mma_i8_ss(d_tmem, da + 2 * j, db + 2 * j, args.idesc, (kb | j) != 0);
+                        else
+                            ptx::mma_f16_ss(d_tmem, da + 2 * j, db + 2 * j, args.idesc, (kb | j) != 0);
+                    }
+                    ptx::mma_commit(empty_bar(s));
+                    if(kb == num_kb - 1) ptx::mma_commit(tfull_bar(as));
+                }
+                __syncwarp();
+                if(++s == SS_STAGES) { s = 0; ph ^= 1; }
+            }
+            if(++as == 2) { as = 0; aph ^= 1; }
+        }
+    }
+    else if(warp >= 4)
+    {
+        // ===================== epilogue =====================
+        const int q = warp & 3;
+        int as = 0;
+        uint32_t aph = 0;
+        for(int t = blockIdx.x; t < num_tiles; t += gridDim.x)
+        {
+            int mb, nb;
+            tile_coord(t, args.num_m_blk, args.num_n_blk, mb, nb);
+            ptx::mbar_wait(tfull_bar(as), aph);
+            ptx::tcgen05_fence_after_sync();
+            const int m          = mb * SS_BM + q * 32 + lane;
+            const uint32_t taddr = tmem_base + as * SS_BN + (uint32_t(q * 32) << 16);
+#pragma unroll 1
+            for(int c = 0; c < SS_BN / 32; ++c)
+            {
+                uint32_t r[32];
+                ptx::tmem_ld_x32(taddr + c * 32, r);
+                ptx::tmem_ld_wait();
+                ss_epilogue_chunk(args, m, nb * SS_BN + c * 32, r);
+            }
+            ptx::tcgen05_fence_before_sync();
+            __syncwarp();
+            if(lane == 0) ptx::mbar_arrive(tempty_bar(as));
+            if(++as == 2) { as = 0; aph ^= 1; }
+        }
+    }
+
+    ptx::tcgen05_fence_before_sync();
+    __syncthreads();
+    if(warp == 2)
+    {
+        ptx::tcgen05_fence_after_sync();
+        ptx::tmem_dealloc<512>(tmem_base);
+    }
+}
+
+} // namespace
+
+// ---------------------------------------------------------------------------------------------
+int plan_gemm_ss(const ckb_gemm_problem& p, ckb_gemm_plan& plan)
+{
+    const bool i8 = p.a_dtype == CKB_I8;
+    const int eb  = dtype_bytes(p.a_dtype);
+    SSPlan* sp    = reinterpret_cast<SSPlan*>(plan.opaque);
+    static_assert(sizeof(SSPlan) <= sizeof(plan.opaque), "opaque too small");
+    const CUtensorMapDataType dt = i8 ? CU_TENSOR_MAP_DATA_TYPE_UINT8
+                                      : (p.a_dtype == CKB_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
+                                                               : CU_TENSOR_MAP_DATA_TYPE_FLOAT16);
+    const uint32_t box_k = SS_BK_BYTES / eb;
+    if(int rc = encode_tmap_2d(&sp->tmA, dt, eb, p.a, p.M, p.K, p.lda, SS_BM, box_k, CU_TENSOR_MAP_SWIZZLE_128B)) return rc;
+    if(int rc = encode_tmap_2d(&sp->tmB, dt, eb, p.b, p.N, p.K, p.ldb, SS_BN, box_k, CU_TENSOR_MAP_SWIZZLE_128B)) return rc;
+    const int num_m_blk = (p.M + SS_BM - 1) / SS_BM, num_n_blk = (p.N + SS_BN - 1) / SS_BN;
+    plan.grid       = std::max(1, std::min(device_info().sm_count > 0 ? device_info().sm_count : 148, num_m_blk * num_n_blk));
+    plan.block      = SS_THREADS;
+    plan.smem_bytes = SS_SMEM;
+    plan.workspace_bytes = 0;
+    plan.split_units     = 1;
+    snprintf(plan.kernel_name, sizeof plan.kernel_name, "gemm_ss_%s_tcgen05_128x256x%d_s%d",
+             i8 ? "i8" : (p.a_dtype == CKB_BF16 ? "bf16" : "f16"), int(box_k), SS_STAGES);
+    return CKB_OK;
+}
+
+static void fill_epi(const ckb_gemm_problem& p, EpiParams& ep)
+{
+    ep.cde_op = p.cde_op; ep.act = p.act; ep.scale = p.cde_scale; ep.flags = p.flags;
+    ep.num_d = p.num_d;
+    for(int i = 0; i < CKB_MAX_D; ++i)
+    {
+        ep.d_dtype[i] = p.d_dtype[i]; ep.d[i] = p.d[i]; ep.d_sm[i] = p.d_sm[i]; ep.d_sn[i] = p.d_sn[i];
+    }
+    ep.e_dtype = p.e_dtype; ep.e = p.e; ep.lde = p.lde; ep.M = p.M; ep.N = p.N;
+}
+void fill_epi_params(const ckb_gemm_problem& p, EpiParams& ep) { fill_epi(p, ep); }
+
+int run_gemm_ss(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStream_t stream)
+{
+    const SSPlan* sp = reinterpret_cast<const SSPlan*>(plan.opaque);
+    const bool i8    = p.a_dtype == CKB_I8;
+    const int eb     = dtype_bytes(p.a_dtype);
+    SSArgs a{};
+    a.M = p.M; a.N = p.N;
+    a.kb_elems  = SS_BK_BYTES / eb;
+    a.num_kb    = (p.K + a.kb_elems - 1) / a.kb_elems;
+    a.num_m_blk = (p.M + SS_BM - 1) / SS_BM;
+    a.num_n_blk = (p.N + SS_BN - 1) / SS_BN;
+    a.is_i8     = i8;
+    a.idesc     = i8 ? ptx::make_idesc(2, 1, 1, SS_BM, SS_BN)
+                     : ptx::make_idesc(1, p.a_dtype == CKB_BF16 ? 1 : 0, p.a_dtype == CKB_BF16 ? 1 : 0, SS_BM, SS_BN);
+    fill_epi(p, a.ep);
+    static bool attr_set = false;
+    if(!attr_set)
+    {
+        CKB_CUDA_CHECK(cudaFuncSetAttribute(gemm_ss_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SS_SMEM));
+        attr_set = true;
+    }
+    gemm_ss_kernel<<<plan.grid, SS_THREADS, SS_SMEM, stream>>>(sp->tmA, sp->tmB, a);
+    CKB_CUDA_CHECK(cudaGetLastError());
+    return CKB_OK;
+}
+
+} // namespace ckb

@@ -1,0 +1,48 @@
+// kernels.h -- internal interface between the C-ABI front end (api.cu) and the kernel families.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <algorithm>
+
+#include "../../include/ckb.h"
+
+namespace ckb {
+
+struct EpiParams;
+void fill_epi_params(const ckb_gemm_problem& p, EpiParams& ep);
+
+enum KernelId : int32_t {
+    KID_NONE       = 0,
+    KID_GEMM_SS    = 1, // K3: TMA + tcgen05 SS (int8 x int8 -> s32, bf16/f16 dense)
+    KID_WQ_DECODE  = 2, // K2: weight-dequant -> TMEM A operand, stream-K, M <= 64
+    KID_WQ_PREFILL = 3  // K1: weight-dequant -> TMEM A operand, persistent tiles
+};
+
+// ---- K3 ---------------------------------------------------------------------------------------
+struct SSPlan
+{
+    CUtensorMap tmA, tmB;
+};
+int plan_gemm_ss(const ckb_gemm_problem& p, ckb_gemm_plan& plan);
+int run_gemm_ss(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStream_t stream);
+
+// ---- K1 / K2 ----------------------------------------------------------------------------------
+struct WQPlan
+{
+    CUtensorMap tmAct; // activations A[M][K] (MMA B operand)
+    CUtensorMap tmW;   // plain int8/u8 weights [N][K] (unused for pre-packed int4)
+    int32_t n_mma;     // MMA N (padded M tile)
+    int32_t units_total, units_per_tile;
+};
+int plan_wq_decode(const ckb_gemm_problem& p, ckb_gemm_plan& plan);
+int run_wq_decode(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, void* workspace, cudaStream_t stream);
+int plan_wq_prefill(const ckb_gemm_problem& p, ckb_gemm_plan& plan);
+int run_wq_prefill(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, void* workspace, cudaStream_t stream);
+
+// ---- pre-pack ---------------------------------------------------------------------------------
+int launch_prepack_u8(const void* src, void* dst, long long n, cudaStream_t stream);
+int launch_prepack_int4(const void* src, long long sk, long long sn, int N, int K, void* dst, cudaStream_t stream);
+int launch_transpose_i8(const void* src, long long ld_src, int rows, int cols, void* dst, long long ld_dst, cudaStream_t stream);
+
+} // namespace ckb
