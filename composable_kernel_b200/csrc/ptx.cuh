@@ -73,6 +73,22 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity)
     return ok != 0;
 }
 
+// non-blocking probe (try_wait may suspend the thread for a hardware time limit when the phase is pending)
+__device__ __forceinline__ bool mbar_test_wait(uint32_t bar, uint32_t parity)
+{
+    uint32_t ok;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred P;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 P, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, P;\n\t"
+        "}\n"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+
 // Bounded wait: a protocol bug becomes a trap (launch error) instead of a hung GPU.
 #ifndef CKB_WAIT_TIMEOUT_NS
 #define CKB_WAIT_TIMEOUT_NS 4000000000ull
@@ -91,6 +107,96 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
             __trap();
         }
     }
+}
+
+// Probe several barriers in ONE asm block so the (~90-cycle) try_wait latencies overlap instead of
+// chaining (each selp would otherwise stall in-order issue behind its own try_wait).
+__device__ __forceinline__ uint32_t mbar_try_wait2(uint32_t b0, uint32_t p0, uint32_t b1, uint32_t p1)
+{
+    uint32_t ok;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred P0, P1;\n\t"
+        ".reg .b32 r0, r1;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P0, [%1], %2;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%3], %4;\n\t"
+        "selp.u32 r0, 1, 0, P0;\n\t"
+        "selp.u32 r1, 2, 0, P1;\n\t"
+        "or.b32 %0, r0, r1;\n\t"
+        "}\n"
+        : "=r"(ok)
+        : "r"(b0), "r"(p0), "r"(b1), "r"(p1)
+        : "memory");
+    return ok;
+}
+__device__ __forceinline__ uint32_t
+mbar_try_wait3(uint32_t b0, uint32_t p0, uint32_t b1, uint32_t p1, uint32_t b2, uint32_t p2)
+{
+    uint32_t ok;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred P0, P1, P2;\n\t"
+        ".reg .b32 r0, r1, r2;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P0, [%1], %2;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%3], %4;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P2, [%5], %6;\n\t"
+        "selp.u32 r0, 1, 0, P0;\n\t"
+        "selp.u32 r1, 2, 0, P1;\n\t"
+        "selp.u32 r2, 4, 0, P2;\n\t"
+        "or.b32 r0, r0, r1;\n\t"
+        "or.b32 %0, r0, r2;\n\t"
+        "}\n"
+        : "=r"(ok)
+        : "r"(b0), "r"(p0), "r"(b1), "r"(p1), "r"(b2), "r"(p2)
+        : "memory");
+    return ok;
+}
+// six NON-BLOCKING probes in one block (test_wait: try_wait would suspend the thread on a pending
+// barrier for a hardware time limit); bit k set = barrier k already complete
+__device__ __forceinline__ uint32_t mbar_test_wait6(const uint32_t* b, const uint32_t* p)
+{
+    uint32_t ok;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred P0, P1, P2, P3, P4, P5;\n\t"
+        ".reg .b32 r0, r1, r2, r3, r4, r5;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 P0, [%1], %2;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 P1, [%3], %4;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 P2, [%5], %6;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 P3, [%7], %8;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 P4, [%9], %10;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 P5, [%11], %12;\n\t"
+        "selp.u32 r0, 1, 0, P0;\n\t"
+        "selp.u32 r1, 2, 0, P1;\n\t"
+        "selp.u32 r2, 4, 0, P2;\n\t"
+        "selp.u32 r3, 8, 0, P3;\n\t"
+        "selp.u32 r4, 16, 0, P4;\n\t"
+        "selp.u32 r5, 32, 0, P5;\n\t"
+        "or.b32 r0, r0, r1;\n\t"
+        "or.b32 r2, r2, r3;\n\t"
+        "or.b32 r4, r4, r5;\n\t"
+        "or.b32 r0, r0, r2;\n\t"
+        "or.b32 %0, r0, r4;\n\t"
+        "}\n"
+        : "=r"(ok)
+        : "r"(b[0]), "r"(p[0]), "r"(b[1]), "r"(p[1]), "r"(b[2]), "r"(p[2]), "r"(b[3]), "r"(p[3]), "r"(b[4]),
+          "r"(p[4]), "r"(b[5]), "r"(p[5])
+        : "memory");
+    return ok;
+}
+__device__ __forceinline__ void mbar_wait2(uint32_t b0, uint32_t p0, uint32_t b1, uint32_t p1)
+{
+    const uint32_t ok = mbar_try_wait2(b0, p0, b1, p1);
+    if(!(ok & 1)) mbar_wait(b0, p0);
+    if(!(ok & 2)) mbar_wait(b1, p1);
+}
+__device__ __forceinline__ void
+mbar_wait3(uint32_t b0, uint32_t p0, uint32_t b1, uint32_t p1, uint32_t b2, uint32_t p2)
+{
+    const uint32_t ok = mbar_try_wait3(b0, p0, b1, p1, b2, p2);
+    if(!(ok & 1)) mbar_wait(b0, p0);
+    if(!(ok & 2)) mbar_wait(b1, p1);
+    if(!(ok & 4)) mbar_wait(b2, p2);
 }
 
 // ------------------------------------------------------------------ proxies / fences
