@@ -69,6 +69,28 @@ __device__ __forceinline__ void dequant_w4_word(uint32_t w, uint32_t zmagic, uin
     }
 }
 
+__device__ __forceinline__ uint32_t hmul2_bf16(uint32_t a, uint32_t b)
+{
+    uint32_t r;
+    asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+    return r;
+}
+// W4 with the (k-group, n) scale folded in before the MMA: round_to_nearest_A( (q - zp) * s ).
+// (q - zp) is exact in A's type and the product of two 8/11-bit significands is exact in fp32, so the
+// packed multiply performs exactly ONE rounding -- the [EXT] analogue of CK's Multiply B-functor /
+// fpAintB converter, which also round q*s once into A's type before the MMA.
+template <bool F16>
+__device__ __forceinline__ void dequant_w4_word_scaled(uint32_t w, uint32_t zmagic, uint32_t scale2, uint32_t* out4)
+{
+    constexpr uint32_t MAGIC = F16 ? 0x64006400u : 0x43004300u;
+#pragma unroll
+    for(int i = 0; i < 4; ++i)
+    {
+        const uint32_t t = lop3<0xEA>(w >> (4 * i), 0x000F000Fu, MAGIC);
+        out4[i] = F16 ? hmul2_f16(hsub2_f16(t, zmagic), scale2) : hmul2_bf16(hsub2_bf16(t, zmagic), scale2);
+    }
+}
+
 // ---- W8 fpAintB (fp16): u8 -> 0x6400|u8 = 1024 + u8; minus 1152 (= 0x6480) removes the +128 bias
 // (the reference's own trick, unary_element_wise_operation.hpp:1061-1091); times scale: ONE rounding.
 __device__ __forceinline__ void dequant_u8x4_fpaintb(uint32_t w, uint32_t scale2, uint32_t* out2)

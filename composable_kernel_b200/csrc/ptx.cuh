@@ -93,9 +93,10 @@ __device__ __forceinline__ bool mbar_test_wait(uint32_t bar, uint32_t parity)
 #ifndef CKB_WAIT_TIMEOUT_NS
 #define CKB_WAIT_TIMEOUT_NS 4000000000ull
 #endif
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+// slow path kept out of line: the printf/trap sequence is large and would otherwise be replicated at
+// every wait site (instruction-cache footprint is what limits the warp-specialised kernels)
+static __device__ __noinline__ void mbar_wait_slow(uint32_t bar, uint32_t parity)
 {
-    if(mbar_try_wait(bar, parity)) return;
     const uint64_t t0 = global_timer_ns();
     uint32_t spins    = 0;
     while(!mbar_try_wait(bar, parity))
@@ -107,6 +108,11 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
             __trap();
         }
     }
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    if(mbar_try_wait(bar, parity)) return;
+    mbar_wait_slow(bar, parity);
 }
 
 // Probe several barriers in ONE asm block so the (~90-cycle) try_wait latencies overlap instead of

@@ -5,27 +5,25 @@
 // Roles are swapped with respect to CK (whose kernels put the weight on the B side of the MFMA):
 // the WEIGHT is the tcgen05 A operand (MMA-M = 128 output channels n) and the ACTIVATIONS are the
 // tcgen05 B operand (MMA-N = padded M), so one CTA streams 128 channels x K of weights.
-//   * weights: HBM --TMA/bulk copy--> smem ring --ld.shared--> registers --unpack/dequant-->
-//     tcgen05.st --> TMEM (A operand; no second trip through shared memory)
-//   * activations: TMA, 128B swizzle, K-major tcgen05 B operand
-//   * accumulators: fp32 in TMEM, drained once per 128-k unit and combined in registers with the
-//     (k-group, n) scale -- exactly the K-blocked scale placement of CK's ab_scale GEMM
-//     (grid/gridwise_gemm_xdl_cshuffle_v3_multi_d_ab_scale.hpp), here with ScaleBlockK = 128.
+//   * weights: HBM --bulk copy / TMA--> smem ring --ld.shared--> registers --unpack, (q-zp)*scale-->
+//     tcgen05.st --> TMEM (the MMA A operand; the dequantised tile never returns to shared memory)
+//   * activations: TMA, 128B swizzle, K-major tcgen05 B operand, own small smem ring
+//   * accumulator: fp32 in TMEM for a whole (tile, K-range) segment, double buffered
 //   * stream-K: the (n-tile, k-unit) space is cut into gridDim.x equal contiguous ranges
 //     (BlockToCTileMap_GemmStreamK, grid/block_to_ctile_map.hpp:1016-1400); partial tiles are reduced
 //     with fp32 red.add into a workspace and finished by the last arriving CTA
 //     (StreamKReductionStrategy::Atomic + the fix-up of DeviceGemm_Xdl_CShuffleV3R1's reduce kernel).
 // Replaces kernel_fpAintB_gemm_wmma / kernel_gemm_xdl_cshuffle_v3 (multi-ABD) for M <= 64.
 //
-// Warp roles (one CTA per SM):
-//   warp 0        producer: bulk/TMA copies of weight units and activation boxes into the smem ring
-//   warp 1        MMA issuer (one lane): 8 x tcgen05.mma (128 x N_MMA x 16) per unit, one commit
-//   warp 2        TMEM allocator
-//   warps 4-7     epilogue: per unit tcgen05.ld of the partial accumulator, acc += scale * partial
-//   warps 8..     dequant teams (4 warps each, TEAMS teams): team t owns units t, t+TEAMS, ...
-// Barriers per unit: full[s] (bytes landed) -> team: wread[s] (smem read), afull[a] (TMEM A written)
-//   -> MMA: mma_done[s] (commit) -> producer (slot free), team (A stage free), epilogue (D ready)
-//   -> epilogue: dempty[b].
+// The pipeline is latency- rather than issue-bound (each barrier hand-off costs 100-400 cycles), so
+// the design keeps the per-CTA pipeline short and runs TWO CTAs per SM:
+//   warps 0 .. 4T-1  dequant teams (T teams of 4 warps; team t owns units t, t+T, ...; the team that
+//                    dequantised a segment's last unit also drains the accumulator and runs the epilogue)
+//   warp  4T         MMA issuer (+ TMEM allocation)
+//   warp  4T+1       producer (bulk / TMA copies)
+// Barriers: wfull[s] -> team -> wread[s] (weight slot free) ; team -> afull[a] ; actfull[t] ;
+//           MMA commit -> mdone[m] (TMEM A stage + activation slot free) and, at a segment end, dfull[d];
+//           epilogue -> dempty[d].
 #include "common.cuh"
 #include "dequant.cuh"
 #include "epilogue.cuh"
@@ -35,18 +33,14 @@
 namespace ckb {
 namespace {
 
-constexpr int DQ_UNIT_N = 128;
-constexpr int DQ_UNIT_K = 128;
-constexpr int DQ_DBUF   = 4; // TMEM accumulator buffers
-constexpr int DQ_TEAMS  = 3; // dequant teams
-constexpr int DQ_THREADS = 256 + 128 * DQ_TEAMS;
-// Warp numbering matters: the SM's warp arbiter favours HIGH warp ids, so the latency-critical
-// single-thread roles (MMA issuer, producer) sit above the ALU-heavy dequant teams.
-constexpr int DQ_WARP_DQ0  = 0;
-constexpr int DQ_WARP_EPI0 = 4 * DQ_TEAMS;
-constexpr int DQ_WARP_MMA  = DQ_WARP_EPI0 + 4;
-constexpr int DQ_WARP_PROD = DQ_WARP_EPI0 + 5;
-constexpr int DQ_WARP_TMEM = DQ_WARP_EPI0 + 6;
+constexpr int DQ_UNIT_N  = 128;
+constexpr int DQ_UNIT_K  = 128;
+constexpr int DQ_TEAMS   = 2;
+constexpr int DQ_THREADS = 128 * DQ_TEAMS + 64;
+constexpr int DQ_WARP_MMA  = 4 * DQ_TEAMS;
+constexpr int DQ_WARP_PROD = 4 * DQ_TEAMS + 1;
+constexpr int DQ_MD        = 4;   // ring of per-unit "MMAs complete" barriers
+constexpr int DQ_TMEM_COLS = 256; // two CTAs per SM
 
 struct DQArgs
 {
@@ -60,23 +54,20 @@ struct DQArgs
     float* ws;               // [n_tiles][N_MMA][128] fp32, zero on entry and on exit
     int* counters;           // [n_tiles], zero on entry and on exit
     uint32_t idesc;
-    long long* trace; // debug timeline (CKB_TRACE), null in production
+    long long* trace;        // debug timeline (CKB_TRACE), null in production
     EpiParams ep;
 };
 
 __host__ __device__ constexpr int dq_w_bytes(int wf) { return wf == WF_W4_GROUP ? 8192 : 16384; }
-__host__ __device__ constexpr int dq_ast(int n_mma) { return n_mma <= 32 ? 6 : 4; }
-// two smem rings: weights (released as soon as the dequant team has read them) and activations
-// (released when the unit's MMAs have completed).  The weight ring is what keeps HBM busy.
-__host__ __device__ constexpr int dq_wst(int wf) { return wf == WF_W4_GROUP ? 16 : 8; }
-__host__ __device__ constexpr int dq_actst(int n_mma) { return n_mma <= 16 ? 8 : 4; }
-constexpr int DQ_MD = 8; // ring of per-unit "MMAs done" barriers
+__host__ __device__ constexpr int dq_ast(int n_mma) { return n_mma <= 32 ? 3 : 2; }   // TMEM A stages
+__host__ __device__ constexpr int dq_wst(int wf) { return wf == WF_W4_GROUP ? 10 : 5; } // 80 KB of weights in flight
+__host__ __device__ constexpr int dq_actst(int n_mma) { return n_mma <= 32 ? 4 : 2; }
 __host__ __device__ constexpr int dq_smem_bytes(int n_mma, int wf)
 {
     return dq_actst(n_mma) * n_mma * 256 + dq_wst(wf) * dq_w_bytes(wf) + 1024 /*barriers*/ + 1024 /*align*/;
 }
 
-__device__ __forceinline__ void store_one(const EpiParams& ep, int m, int n, float acc)
+static __device__ __noinline__ void store_one(const EpiParams& ep, int m, int n, float acc)
 {
     float d0 = 0.f, d1 = 0.f;
     if(ep.num_d > 0) d0 = load_d_f32(ep.d_dtype[0], ep.d[0], (long long)m * ep.d_sm[0] + (long long)n * ep.d_sn[0]);
@@ -89,10 +80,14 @@ __device__ __forceinline__ void store_one(const EpiParams& ep, int m, int n, flo
 }
 
 // debug timeline: role r, unit i, slot k  (only block 0 records; 64 units max)
-#define CKB_TR(r, i, k)                                                                   \
-    do {                                                                                  \
-        if(args.trace && blockIdx.x == 0 && (i) < 64) args.trace[((r)*64 + (i)) * 4 + (k)] = clock64(); \
+#ifdef CKB_ENABLE_TRACE
+#define CKB_TR(r, i, k)                                                                                   \
+    do {                                                                                                  \
+        if(args.trace && blockIdx.x == 0 && (i) < 64) args.trace[((r)*64 + (i)) * 4 + (k)] = clock64();   \
     } while(0)
+#else
+#define CKB_TR(r, i, k) do { } while(0)
+#endif
 
 // ring position helper: advance by `step` without integer division
 struct Ring
@@ -102,48 +97,118 @@ struct Ring
     __device__ __forceinline__ void advance(int step, int size)
     {
         s += step;
-        if(s >= size) { s -= size; ph ^= 1; }
+        while(s >= size) { s -= size; ph ^= 1; }
     }
 };
 
+// Segment epilogue, deliberately NOT inlined and not unrolled: it runs once per (CTA, tile) and its
+// code (all CDE functors x all dtypes) must stay out of the hot loops' instruction-cache footprint.
+//   wait for the segment's MMAs, TMEM -> registers, then either the CDE epilogue (whole K range owned)
+//   or the stream-K reduction: fp32 red.add into the workspace, last arriving CTA finishes the tile.
+template <int N_MMA>
+static __device__ __noinline__ void decode_drain(const DQArgs& args, int nt, int kg, int nt0, int kg0, uint32_t tmem_d0,
+                                          uint32_t dfull0, uint32_t dempty0, volatile int* flag, int bar_id, int q,
+                                          int lane)
+{
+    const EpiParams& ep = args.ep;
+    const int row       = q * 32 + lane;
+    const int sidx      = nt - nt0;
+    const int d         = sidx & 1;
+    const int kg_first  = (nt == nt0) ? kg0 : 0;
+    const int seg_units = kg - kg_first + 1;
+    const int k_units   = args.k_units;
+    ptx::mbar_wait(dfull0 + 8u * d, (sidx >> 1) & 1);
+    ptx::tcgen05_fence_after_sync();
+    float acc[N_MMA];
+    const uint32_t taddr = tmem_d0 + d * N_MMA + (uint32_t(q * 32) << 16);
+#pragma unroll
+    for(int c = 0; c < N_MMA; c += 16)
+    {
+        uint32_t v[16];
+        ptx::tmem_ld_x16(taddr + c, v);
+        ptx::tmem_ld_wait();
+#pragma unroll
+        for(int j = 0; j < 16; ++j) acc[c + j] = __uint_as_float(v[j]);
+    }
+    ptx::tcgen05_fence_before_sync();
+    __syncwarp();
+    if(lane == 0) ptx::mbar_arrive(dempty0 + 8u * d);
+    const int n    = nt * DQ_UNIT_N + row;
+    const int mmax = min(args.M, N_MMA);
+    if(seg_units == k_units)
+    {
+        if(n < args.N)
+        {
+#pragma unroll 1
+            for(int j = 0; j < mmax; ++j) store_one(ep, j, n, acc[j]);
+        }
+        return;
+    }
+    float* ws = args.ws + ((size_t)nt * N_MMA) * DQ_UNIT_N + row;
+#pragma unroll 1
+    for(int j = 0; j < mmax; ++j) ptx::red_add_f32(ws + j * DQ_UNIT_N, acc[j]);
+    __threadfence();
+    ptx::named_bar_sync(bar_id, 128);
+    if(q == 0 && lane == 0)
+    {
+        const int old = atomicAdd(args.counters + nt, seg_units);
+        *flag         = (old + seg_units == k_units) ? 1 : 0;
+    }
+    ptx::named_bar_sync(bar_id, 128);
+    const int last = *flag;
+    ptx::named_bar_sync(bar_id, 128);
+    if(last)
+    {
+        __threadfence();
+#pragma unroll 1
+        for(int j = 0; j < mmax; ++j)
+        {
+            const float v = __ldcg(ws + j * DQ_UNIT_N);
+            __stcg(ws + j * DQ_UNIT_N, 0.f);
+            if(n < args.N) store_one(ep, j, n, v);
+        }
+        if(q == 0 && lane == 0) args.counters[nt] = 0;
+    }
+}
+
 template <int N_MMA, int WF, bool F16>
-__global__ void __launch_bounds__(DQ_THREADS, 1)
+__global__ void __launch_bounds__(DQ_THREADS, 2)
 wq_decode_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constant__ CUtensorMap tmW,
                  const DQArgs args)
 {
-    constexpr int ACT_BYTES   = N_MMA * 256; // two boxes of [N_MMA][64 k] 16-bit
-    constexpr int W_BYTES     = dq_w_bytes(WF);
-    constexpr int WST         = dq_wst(WF);      // weight ring stages
-    constexpr int ACT_ST      = dq_actst(N_MMA); // activation ring stages
-    constexpr int AST         = dq_ast(N_MMA);   // TMEM A-operand stages (64 columns each)
-    constexpr int TMEM_COLS   = 512;
-    constexpr int D_COL0      = AST * 64;
-    constexpr bool GROUP      = (WF == WF_W4_GROUP);
-    static_assert(WST >= DQ_TEAMS && DQ_MD >= AST && DQ_MD % ACT_ST == 0 && AST * 64 + DQ_DBUF * N_MMA <= 512,
+    constexpr int ACT_BYTES = N_MMA * 256; // two boxes of [N_MMA][64 k] 16-bit
+    constexpr int W_BYTES   = dq_w_bytes(WF);
+    constexpr int WST       = dq_wst(WF);      // weight ring stages
+    constexpr int ACT_ST    = dq_actst(N_MMA); // activation ring stages
+    constexpr int AST       = dq_ast(N_MMA);   // TMEM A-operand stages (64 columns each)
+    constexpr int D_COL0    = AST * 64;        // two accumulators of N_MMA columns follow
+    constexpr bool GROUP    = (WF == WF_W4_GROUP);
+    static_assert(WST >= DQ_TEAMS && DQ_MD >= AST && DQ_MD % ACT_ST == 0 && AST * 64 + 2 * N_MMA <= DQ_TMEM_COLS,
                   "ring/TMEM budget");
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem            = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     const uint32_t smem_base = ptx::smem_u32(smem);
-    const uint32_t act_base  = smem_base;                       // [ACT_ST][ACT_BYTES]
-    const uint32_t w_base    = smem_base + ACT_ST * ACT_BYTES;  // [WST][W_BYTES]
+    const uint32_t act_base  = smem_base;                      // [ACT_ST][ACT_BYTES]
+    const uint32_t w_base    = smem_base + ACT_ST * ACT_BYTES; // [WST][W_BYTES]
     constexpr int BAR_OFF    = ACT_ST * ACT_BYTES + WST * W_BYTES;
     const uint32_t bar_base  = smem_base + BAR_OFF;
-    auto wfull_bar   = [&](int s) { return bar_base + 8u * s; };          // weights landed
-    auto wread_bar   = [&](int s) { return bar_base + 8u * (16 + s); };   // weights read by the team
-    auto actfull_bar = [&](int t) { return bar_base + 8u * (32 + t); };   // activations landed
-    auto mdone_bar   = [&](int m) { return bar_base + 8u * (40 + m); };   // unit's MMAs complete
-    auto afull_bar   = [&](int a) { return bar_base + 8u * (48 + a); };   // TMEM A stage written
-    auto dempty_bar  = [&](int b) { return bar_base + 8u * (56 + b); };   // TMEM D buffer drained
-    const uint32_t tmem_slot = bar_base + 8u * 60;
-    volatile int* flag_smem  = reinterpret_cast<volatile int*>(smem + BAR_OFF + 8 * 61);
+    auto wfull_bar   = [&](int s) { return bar_base + 8u * s; };        // weights landed
+    auto wread_bar   = [&](int s) { return bar_base + 8u * (16 + s); }; // weights read by the team
+    auto actfull_bar = [&](int t) { return bar_base + 8u * (32 + t); }; // activations landed
+    auto mdone_bar   = [&](int m) { return bar_base + 8u * (36 + m); }; // unit's MMAs complete
+    auto afull_bar   = [&](int a) { return bar_base + 8u * (40 + a); }; // TMEM A stage written
+    auto dfull_bar   = [&](int d) { return bar_base + 8u * (44 + d); }; // segment accumulated
+    auto dempty_bar  = [&](int d) { return bar_base + 8u * (46 + d); }; // accumulator drained
+    const uint32_t tmem_slot = bar_base + 8u * 48;
+    volatile int* flag_smem  = reinterpret_cast<volatile int*>(smem + BAR_OFF + 8 * 50); // one int per team
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
 
-    if(warp == DQ_WARP_PROD && lane == 0) ptx::prefetch_tmap(&tmAct);
-    if(warp == DQ_WARP_MMA && lane == 0)
+    if(warp == DQ_WARP_PROD && lane == 0)
     {
+        ptx::prefetch_tmap(&tmAct);
         for(int s = 0; s < WST; ++s)
         {
             ptx::mbar_init(wfull_bar(s), 1);
@@ -152,12 +217,16 @@ wq_decode_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constan
         for(int t = 0; t < ACT_ST; ++t) ptx::mbar_init(actfull_bar(t), 1);
         for(int m = 0; m < DQ_MD; ++m) ptx::mbar_init(mdone_bar(m), 1);
         for(int a = 0; a < AST; ++a) ptx::mbar_init(afull_bar(a), 4);
-        for(int b = 0; b < DQ_DBUF; ++b) ptx::mbar_init(dempty_bar(b), 4);
+        for(int d = 0; d < 2; ++d)
+        {
+            ptx::mbar_init(dfull_bar(d), 1);
+            ptx::mbar_init(dempty_bar(d), 4);
+        }
         ptx::fence_mbar_init();
     }
-    if(warp == DQ_WARP_TMEM)
+    if(warp == DQ_WARP_MMA)
     {
-        ptx::tmem_alloc<TMEM_COLS>(tmem_slot);
+        ptx::tmem_alloc<DQ_TMEM_COLS>(tmem_slot);
         ptx::tmem_relinquish();
     }
     ptx::tcgen05_fence_before_sync();
@@ -173,6 +242,10 @@ wq_decode_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constan
     const int k_units       = args.k_units;
     const int nt0           = int(u_begin / k_units); // first tile / k-unit of this CTA (one division)
     const int kg0           = int(u_begin - (long long)nt0 * k_units);
+    auto adv = [&](int& nt_, int& kg_, int step) {
+        kg_ += step;
+        while(kg_ >= k_units) { kg_ -= k_units; ++nt_; }
+    };
 
     if(warp == DQ_WARP_PROD)
     {
@@ -182,22 +255,22 @@ wq_decode_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constan
             const uint64_t pol_stream = ptx::policy_evict_first();
             int ntw = nt0, kgw = kg0; // weight cursor
             int nta = nt0, kga = kg0; // activation cursor
-            auto adv = [&](int& nt_, int& kg_) { if(++kg_ == k_units) { kg_ = 0; ++nt_; } };
             auto issue_w = [&](int s) {
                 ptx::mbar_arrive_expect_tx(wfull_bar(s), W_BYTES);
                 if(GROUP)
                     ptx::bulk_load_1d(w_base + s * W_BYTES, args.w_packed + ((size_t)ntw * k_units + kgw) * W_BYTES,
                                       W_BYTES, wfull_bar(s), pol_stream);
                 else
-                    ptx::tma_load_2d_hint(w_base + s * W_BYTES, &tmW, wfull_bar(s), kgw * DQ_UNIT_K, ntw * DQ_UNIT_N, pol_stream);
-                adv(ntw, kgw);
+                    ptx::tma_load_2d_hint(w_base + s * W_BYTES, &tmW, wfull_bar(s), kgw * DQ_UNIT_K, ntw * DQ_UNIT_N,
+                                          pol_stream);
+                adv(ntw, kgw, 1);
             };
             auto issue_a = [&](int t) {
                 const uint32_t st = act_base + t * ACT_BYTES;
                 ptx::mbar_arrive_expect_tx(actfull_bar(t), ACT_BYTES);
                 ptx::tma_load_2d(st, &tmAct, actfull_bar(t), kga * DQ_UNIT_K, 0);
                 ptx::tma_load_2d(st + ACT_BYTES / 2, &tmAct, actfull_bar(t), kga * DQ_UNIT_K + 64, 0);
-                adv(nta, kga);
+                adv(nta, kga, 1);
             };
             // weights do not depend on the previous kernel in the stream: fill the weight ring before the
             // programmatic-dependent-launch wait, activations only after it.
@@ -205,11 +278,11 @@ wq_decode_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constan
             for(; iw < min(WST, n_my); ++iw) issue_w(iw);
             ptx::pdl_wait_prior_grids();
             for(; ia < min(ACT_ST, n_my); ++ia) issue_a(ia);
-            Ring rw{0, 0};  // weight slot of unit iw and the parity of its PREVIOUS use's wread phase
-            Ring rt{0, 0};  // activation slot of unit ia
-            Ring rm{0, 0};  // mdone slot of unit ia - ACT_ST
+            Ring rw{0, 0}; // weight slot of unit iw; parity of its previous use's wread phase
+            Ring rt{0, 0}; // activation slot of unit ia
+            Ring rm{0, 0}; // mdone slot of unit ia - ACT_ST
             // Non-blocking polling of both rings: blocking on one could starve the other (the MMA that
-            // frees an activation slot may be waiting for activations this thread has not issued yet).
+            // frees an activation slot may itself be waiting for activations not issued yet).
             while(iw < n_my || ia < n_my)
             {
                 bool progress = false;
@@ -228,89 +301,91 @@ wq_decode_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constan
                     ++ia;
                     progress = true;
                 }
-                if(!progress) __nanosleep(32);
+                if(!progress) __nanosleep(20);
             }
         }
     }
     else if(warp == DQ_WARP_MMA)
     {
-        // ===================== MMA issuer =====================
-        // Warp-uniform loop, one elected lane issues.  afull[a] implies full[s] (the dequant team waited
-        // on it before arriving).  Per-iteration overhead (barrier probe ~100 clk, tcgen05 fence ~140 clk)
-        // is amortised over every unit whose operands are already there (up to 4 per iteration).
-        Ring r{0, 0}, ra{0, 0}, rb{0, 0}, rt{0, 0}; // mdone slot, TMEM A stage, D buffer, activation slot
-        int i = 0;
-        while(i < n_my)
+        // ===================== MMA issuer (warp-uniform loop, one elected lane issues) =====================
+        // A single warp retires roughly one dependent instruction every 4-6 cycles, so this loop is kept
+        // tiny: it is unrolled over lcm(AST, ACT_ST, DQ_MD) units, which turns every ring slot, barrier
+        // address, TMEM column and smem descriptor into a compile-time offset.
+        constexpr int UNR = (AST == 3) ? 12 : 4;
+        static_assert(UNR % AST == 0 && UNR % ACT_ST == 0 && UNR % DQ_MD == 0, "unroll must cover all rings");
+        constexpr uint32_t A_WRAPS_ODD = (UNR / AST) & 1, T_WRAPS_ODD = (UNR / ACT_ST) & 1;
+        const uint64_t db_base = ptx::make_smem_desc_sw128(act_base, 1024);
+        int nt = nt0, kg = kg0;
+        uint32_t outer = 0; // parity of the unrolled-block index
+        for(int i0 = 0; i0 < n_my; i0 += UNR, outer ^= 1)
         {
-            ptx::mbar_wait3(afull_bar(ra.s), ra.ph, dempty_bar(rb.s), rb.ph ^ 1, actfull_bar(rt.s), rt.ph);
-            int nb = 1;
-            if(i + 3 < n_my)
-            {
-                Ring xa = ra, xb = rb;
-                uint32_t bars[6], pars[6];
 #pragma unroll
-                for(int u = 0; u < 3; ++u)
-                {
-                    xa.advance(1, AST);
-                    xb.advance(1, DQ_DBUF);
-                    bars[2 * u] = afull_bar(xa.s);       pars[2 * u] = xa.ph;
-                    bars[2 * u + 1] = dempty_bar(xb.s);  pars[2 * u + 1] = xb.ph ^ 1;
-                }
-                const uint32_t ok = ptx::mbar_test_wait6(bars, pars);
-                if((ok & 3) == 3) { nb = 2; if((ok & 12) == 12) { nb = 3; if((ok & 48) == 48) nb = 4; } }
-            }
-            if(lane == 0) CKB_TR(1, i, 0);
-            ptx::tcgen05_fence_after_sync();
-            for(int u = 0; u < nb; ++u)
+            for(int u = 0; u < UNR; ++u)
             {
-                if(u > 0) ptx::mbar_wait(actfull_bar(rt.s), rt.ph);
-                const uint32_t act    = act_base + rt.s * ACT_BYTES;
-                const uint32_t d_tmem = tmem_base + D_COL0 + rb.s * N_MMA;
-                const uint32_t a_tmem = tmem_base + ra.s * 64;
-                const uint64_t db0    = ptx::make_smem_desc_sw128(act, 1024);
+                const int i = i0 + u;
+                if(i >= n_my) break;
+                constexpr int dummy = 0; (void)dummy;
+                const int a_s = u % AST, t_s = u % ACT_ST, m_s = u % DQ_MD;
+                const uint32_t a_ph = ((u / AST) & 1) ^ (A_WRAPS_ODD & outer);
+                const uint32_t t_ph = ((u / ACT_ST) & 1) ^ (T_WRAPS_ODD & outer);
+                const bool seg_first = (i == 0) || (kg == 0);
+                const bool seg_last  = (i + 1 == n_my) || (kg + 1 == k_units);
+                const int sidx       = nt - nt0; // segment index inside this CTA
+                const int d          = sidx & 1;
+                if(seg_first) ptx::mbar_wait(dempty_bar(d), ((sidx >> 1) & 1) ^ 1);
+                ptx::mbar_wait2(afull_bar(a_s), a_ph, actfull_bar(t_s), t_ph);
+                if(lane == 0) CKB_TR(1, i, 0);
+                ptx::tcgen05_fence_after_sync();
+                const uint32_t d_tmem = tmem_base + D_COL0 + d * N_MMA;
+                const uint32_t a_tmem = tmem_base + a_s * 64;
                 if(ptx::elect_one())
                 {
 #pragma unroll
                     for(int j = 0; j < DQ_UNIT_K / 16; ++j)
                     {
                         // descriptor start address is in 16-byte units: +32 B per k-step, second box after ACT_BYTES/2
-                        const uint64_t db = db0 + uint64_t(((j / 4) * (ACT_BYTES / 2) + (j % 4) * 32) >> 4);
-                        ptx::mma_f16_ts(d_tmem, a_tmem + j * 8, db, args.idesc, j != 0);
+                        const uint64_t db = db_base + uint64_t((t_s * ACT_BYTES + (j / 4) * (ACT_BYTES / 2) + (j % 4) * 32) >> 4);
+                        ptx::mma_f16_ts(d_tmem, a_tmem + j * 8, db, args.idesc, (j != 0 || !seg_first) ? 1u : 0u);
                     }
-                    ptx::mma_commit(mdone_bar(r.s));
+                    ptx::mma_commit(mdone_bar(m_s));
+                    if(seg_last) ptx::mma_commit(dfull_bar(d));
                 }
                 __syncwarp();
-                r.advance(1, DQ_MD);
-                ra.advance(1, AST);
-                rb.advance(1, DQ_DBUF);
-                rt.advance(1, ACT_ST);
+                if(lane == 0) CKB_TR(1, i, 1);
+                if(++kg == k_units) { kg = 0; ++nt; }
             }
-            if(lane == 0) CKB_TR(1, i, 1);
-            i += nb;
         }
     }
-    else if(warp < DQ_WARP_EPI0)
+    else
     {
-        // ===================== dequant teams: smem -> registers -> TMEM (A operand) =====================
-        const int q    = warp & 3;                        // TMEM lane quarter
-        const int team = (warp - DQ_WARP_DQ0) >> 2;
-        const int row  = q * 32 + lane;                   // channel inside the tile
+        // ===================== dequant teams: smem -> registers -> TMEM (A operand); segment epilogue ============
+        const int q    = warp & 3;  // TMEM lane quarter
+        const int team = warp >> 2;
+        const int row  = q * 32 + lane; // channel inside the tile
         const bool tr  = (q == 0 && lane == 0);
         float ch_scale_f   = 1.f;
         uint32_t ch_scale2 = 0;
         int cur_nt = -1;
-        int nt = nt0, kg = kg0 + team;
-        while(kg >= k_units) { kg -= k_units; ++nt; }
+        bool pdl_waited = false;
+
+        auto load_scale2 = [&](int nt_, int kg_) -> uint32_t {
+            const int n_      = min(nt_ * DQ_UNIT_N + row, args.N - 1);
+            const uint32_t sb = __ldg(static_cast<const uint16_t*>(args.scale) + (size_t)kg_ * args.N + n_);
+            return sb | (sb << 16);
+        };
         auto load_zero = [&](int nt_, int kg_) -> int {
+            if(!args.zero) return args.zero_const;
             return int(__ldg(args.zero + (size_t)kg_ * args.N + min(nt_ * DQ_UNIT_N + row, args.N - 1)));
         };
-        int z = args.zero_const;
-        if(GROUP && args.zero && team < n_my) z = load_zero(nt, kg);
-        Ring rw{team, 0};            // weight ring slot of unit i
-        Ring rm{team % DQ_MD, 0};    // mdone ring slot of unit i
-        int a_s = team % AST;
-        for(int i = team; i < n_my; i += DQ_TEAMS)
-        {
+
+        auto drain = [&](int nt, int kg) {
+            if(!pdl_waited) { ptx::pdl_wait_prior_grids(); pdl_waited = true; }
+            decode_drain<N_MMA>(args, nt, kg, nt0, kg0, tmem_base + D_COL0, dfull_bar(0), dempty_bar(0), flag_smem + team,
+                                1 + team, q, lane);
+        };
+
+        // ---- one unit: ring positions are derived from the unit index with compile-time ring sizes ----
+        auto unit = [&](int i, int nt, int kg, uint32_t sc2, int z) {
             if((WF == WF_W8_MUL || WF == WF_W8_FPAINTB) && nt != cur_nt)
             {
                 cur_nt            = nt;
@@ -319,20 +394,14 @@ wq_decode_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constan
                 ch_scale_f        = bf16_bits_to_f32(sb);
                 ch_scale2         = uint32_t(sb) | (uint32_t(sb) << 16);
             }
-            // zero point of this team's NEXT unit: in flight while the current one is processed
-            int nt_n = nt, kg_n = kg + DQ_TEAMS;
-            while(kg_n >= k_units) { kg_n -= k_units; ++nt_n; }
-            int z_next = args.zero_const;
-            if(GROUP && args.zero && i + DQ_TEAMS < n_my) z_next = load_zero(nt_n, kg_n);
-            // previous user of TMEM A stage a_s is unit i - AST: ring slot (r.s - AST) mod STAGES
-            int sp = rm.s - AST;
-            uint32_t php = rm.ph;
-            if(sp < 0) { sp += DQ_MD; php ^= 1; }
-            const bool need_prev = i >= AST;
+            const int ws_slot      = i % WST;
+            const uint32_t ws_ph   = uint32_t(i / WST) & 1;
+            const int a_s          = i % AST;
+            const int ip           = i - AST; // previous user of this TMEM A stage
             if(tr) CKB_TR(2 + team, i, 0);
-            ptx::mbar_wait(wfull_bar(rw.s), rw.ph);
+            ptx::mbar_wait(wfull_bar(ws_slot), ws_ph);
             if(tr) CKB_TR(2 + team, i, 1);
-            const uint8_t* st    = smem + ACT_ST * ACT_BYTES + rw.s * W_BYTES;
+            const uint8_t* st    = smem + ACT_ST * ACT_BYTES + ws_slot * W_BYTES;
             const uint32_t taddr = tmem_base + a_s * 64 + (uint32_t(q * 32) << 16);
             if(GROUP)
             {
@@ -341,19 +410,19 @@ wq_decode_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constan
 #pragma unroll
                 for(int j = 0; j < 4; ++j) c[j] = *reinterpret_cast<const uint4*>(st + j * 2048 + row * 16);
                 __syncwarp();
-                if(lane == 0) ptx::mbar_arrive(wread_bar(rw.s));
+                if(lane == 0) ptx::mbar_arrive(wread_bar(ws_slot));
                 const uint32_t zm = F16 ? (0x6400u + z) * 0x10001u : (0x4300u + z) * 0x10001u;
-                if(need_prev) ptx::mbar_wait(mdone_bar(sp), php);
+                if(ip >= 0) ptx::mbar_wait(mdone_bar(ip % DQ_MD), uint32_t(ip / DQ_MD) & 1);
                 if(tr) CKB_TR(2 + team, i, 2);
                 ptx::tcgen05_fence_after_sync();
 #pragma unroll
                 for(int j = 0; j < 4; ++j)
                 {
                     uint32_t out[16];
-                    dequant_w4_word<F16>(c[j].x, zm, out + 0);
-                    dequant_w4_word<F16>(c[j].y, zm, out + 4);
-                    dequant_w4_word<F16>(c[j].z, zm, out + 8);
-                    dequant_w4_word<F16>(c[j].w, zm, out + 12);
+                    dequant_w4_word_scaled<F16>(c[j].x, zm, sc2, out + 0);
+                    dequant_w4_word_scaled<F16>(c[j].y, zm, sc2, out + 4);
+                    dequant_w4_word_scaled<F16>(c[j].z, zm, sc2, out + 8);
+                    dequant_w4_word_scaled<F16>(c[j].w, zm, sc2, out + 12);
                     ptx::tmem_st_x16(taddr + j * 16, out);
                 }
             }
@@ -365,8 +434,8 @@ wq_decode_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constan
                 for(int j = 0; j < 8; ++j)
                     c[j] = *reinterpret_cast<const uint4*>(st + row * 128 + ((j ^ (row & 7)) * 16));
                 __syncwarp();
-                if(lane == 0) ptx::mbar_arrive(wread_bar(rw.s));
-                if(need_prev) ptx::mbar_wait(mdone_bar(sp), php);
+                if(lane == 0) ptx::mbar_arrive(wread_bar(ws_slot));
+                if(ip >= 0) ptx::mbar_wait(mdone_bar(ip % DQ_MD), uint32_t(ip / DQ_MD) & 1);
                 ptx::tcgen05_fence_after_sync();
 #pragma unroll
                 for(int jj = 0; jj < 8; jj += 2)
@@ -393,181 +462,45 @@ wq_decode_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constan
             __syncwarp();
             if(lane == 0) ptx::mbar_arrive(afull_bar(a_s));
             if(tr) CKB_TR(2 + team, i, 3);
-            rw.advance(DQ_TEAMS, WST);
-            rm.advance(DQ_TEAMS, DQ_MD);
-            a_s += DQ_TEAMS % AST;
-            if(a_s >= AST) a_s -= AST;
-            nt = nt_n; kg = kg_n; z = z_next;
-        }
-    }
-    else if(warp < DQ_WARP_MMA)
-    {
-        // ===================== epilogue: TMEM -> registers, group scale, stream-K reduction =====================
-        ptx::pdl_wait_prior_grids();
-        const int q   = warp & 3;
-        const int row = q * 32 + lane;
-        const bool tr = (q == 0 && lane == 0);
-        const EpiParams& ep = args.ep;
-        float acc[N_MMA];
-#pragma unroll
-        for(int j = 0; j < N_MMA; ++j) acc[j] = 0.f;
-        int seg_units = 0;
-        int nt = nt0, kg = kg0;     // unit being drained
-        int ntp = nt0, kgp = kg0;   // unit whose scale is being prefetched (4 ahead)
-        Ring r{0, 0}, rb{0, 0};
-        auto load_scale = [&](int nt_, int kg_) -> uint16_t {
-            const int n_ = min(nt_ * DQ_UNIT_N + row, args.N - 1);
-            return __ldg(static_cast<const uint16_t*>(args.scale) + (size_t)kg_ * args.N + n_);
-        };
-        auto adv = [&](int& nt_, int& kg_) { if(++kg_ == k_units) { kg_ = 0; ++nt_; } };
-        // group scales come straight from global memory through a 4-deep register ring
-        uint16_t sc_ring[4] = {0, 0, 0, 0};
-#pragma unroll
-        for(int j = 0; j < 4; ++j)
-            if(GROUP && j < n_my) { sc_ring[j] = load_scale(ntp, kgp); adv(ntp, kgp); }
-
-        auto flush = [&]() {
-            const int n = nt * DQ_UNIT_N + row;
-            if(seg_units == k_units)
-            {
-                // this CTA owned the whole K range of the tile: finish directly
-                if(n < args.N)
-                {
-#pragma unroll
-                    for(int j = 0; j < N_MMA; ++j)
-                        if(j < args.M) store_one(ep, j, n, acc[j]);
-                }
-            }
-            else
-            {
-                float* ws = args.ws + ((size_t)nt * N_MMA) * DQ_UNIT_N + row;
-#pragma unroll
-                for(int j = 0; j < N_MMA; ++j)
-                    if(j < args.M) ptx::red_add_f32(ws + j * DQ_UNIT_N, acc[j]);
-                __threadfence();
-                ptx::named_bar_sync(1, 128);
-                if(warp == DQ_WARP_EPI0 && lane == 0)
-                {
-                    const int old = atomicAdd(args.counters + nt, seg_units);
-                    *flag_smem    = (old + seg_units == k_units) ? 1 : 0;
-                }
-                ptx::named_bar_sync(1, 128);
-                const int last = *flag_smem;
-                ptx::named_bar_sync(1, 128);
-                if(last)
-                {
-                    __threadfence();
-#pragma unroll
-                    for(int j = 0; j < N_MMA; ++j)
-                    {
-                        if(j < args.M)
-                        {
-                            const float v = __ldcg(ws + j * DQ_UNIT_N);
-                            __stcg(ws + j * DQ_UNIT_N, 0.f);
-                            if(n < args.N) store_one(ep, j, n, v);
-                        }
-                    }
-                    if(warp == DQ_WARP_EPI0 && lane == 0) args.counters[nt] = 0;
-                }
-            }
-#pragma unroll
-            for(int j = 0; j < N_MMA; ++j) acc[j] = 0.f;
-            seg_units = 0;
-        };
-        auto to_scale = [&](uint16_t bits) -> float {
-            if(!GROUP) return 1.f;
-            return F16 ? __half2float(__ushort_as_half(bits)) : bf16_bits_to_f32(bits);
+            if((i + 1 == n_my) || (kg + 1 == k_units)) drain(nt, kg);
         };
 
-        for(int i0 = 0; i0 < n_my; i0 += 4)
+        // Group scales / zero points come straight from global memory, two team-iterations ahead, through
+        // registers that are only read one full iteration after the load was issued (loop unrolled by 2).
+        int nt = nt0, kg = kg0;
+        adv(nt, kg, team);
+        int ntp = nt, kgp = kg; // prefetch cursor
+        uint32_t scA = 0, scB = 0;
+        int zA = args.zero_const, zB = args.zero_const;
+        if(GROUP)
         {
-#pragma unroll
-            for(int pr = 0; pr < 2; ++pr)
+            if(team < n_my) { scA = load_scale2(ntp, kgp); zA = load_zero(ntp, kgp); }
+            adv(ntp, kgp, DQ_TEAMS);
+            if(team + DQ_TEAMS < n_my) { scB = load_scale2(ntp, kgp); zB = load_zero(ntp, kgp); }
+            adv(ntp, kgp, DQ_TEAMS);
+        }
+        for(int i = team; i < n_my; i += 2 * DQ_TEAMS)
+        {
+            unit(i, nt, kg, scA, zA);
+            adv(nt, kg, DQ_TEAMS);
+            if(GROUP && i + 2 * DQ_TEAMS < n_my) { scA = load_scale2(ntp, kgp); zA = load_zero(ntp, kgp); }
+            adv(ntp, kgp, DQ_TEAMS);
+            if(i + DQ_TEAMS < n_my)
             {
-                const int ia = i0 + 2 * pr;
-                if(ia >= n_my) break;
-                // two units per barrier wait when both belong to the same tile segment (N_MMA == 16 only)
-                const bool pair = (N_MMA == 16) && (ia + 1 < n_my) && (kg + 1 < k_units);
-                Ring r2 = r, rb2 = rb;
-                r2.advance(1, DQ_MD);
-                rb2.advance(1, DQ_DBUF);
-                if(tr) CKB_TR(5, ia, 0);
-                if(pair) ptx::mbar_wait(mdone_bar(r2.s), r2.ph); // MMAs complete in order: unit ia is done too
-                else ptx::mbar_wait(mdone_bar(r.s), r.ph);
-                if(tr) CKB_TR(5, ia, 1);
-                ptx::tcgen05_fence_after_sync();
-                const uint32_t lane_off = uint32_t(q * 32) << 16;
-                if(pair)
-                {
-                    uint32_t v0[16], v1[16];
-                    ptx::tmem_ld_x16(tmem_base + D_COL0 + rb.s * N_MMA + lane_off, v0);
-                    ptx::tmem_ld_x16(tmem_base + D_COL0 + rb2.s * N_MMA + lane_off, v1);
-                    ptx::tmem_ld_wait();
-                    if(tr) CKB_TR(5, ia, 2);
-                    ptx::tcgen05_fence_before_sync();
-                    __syncwarp();
-                    if(lane == 0) { ptx::mbar_arrive(dempty_bar(rb.s)); ptx::mbar_arrive(dempty_bar(rb2.s)); }
-                    const float s0 = to_scale(sc_ring[2 * pr]), s1 = to_scale(sc_ring[2 * pr + 1]);
-#pragma unroll
-                    for(int j = 0; j < 16; ++j) acc[j] = fmaf(s0, __uint_as_float(v0[j]), acc[j]);
-#pragma unroll
-                    for(int j = 0; j < 16; ++j) acc[j] = fmaf(s1, __uint_as_float(v1[j]), acc[j]);
-                    seg_units += 2;
-                    adv(nt, kg);                       // now at unit ia + 1
-                    const bool seg_end = (ia + 2 == n_my) || (kg + 1 == k_units);
-                    if(seg_end) flush();
-                    adv(nt, kg);
-                    r = r2; rb = rb2;
-                    r.advance(1, DQ_MD);
-                    rb.advance(1, DQ_DBUF);
-                }
-                else
-                {
-                    for(int h = 0; h < 2; ++h)
-                    {
-                        const int i = ia + h;
-                        if(i >= n_my) break;
-                        if(h == 1)
-                        {
-                            ptx::mbar_wait(mdone_bar(r.s), r.ph);
-                            ptx::tcgen05_fence_after_sync();
-                        }
-                        const float s0 = to_scale(h == 0 ? sc_ring[2 * pr] : sc_ring[2 * pr + 1]);
-#pragma unroll
-                        for(int c = 0; c < N_MMA; c += 16)
-                        {
-                            uint32_t v[16];
-                            ptx::tmem_ld_x16(tmem_base + D_COL0 + rb.s * N_MMA + c + lane_off, v);
-                            ptx::tmem_ld_wait();
-#pragma unroll
-                            for(int j = 0; j < 16; ++j) acc[c + j] = fmaf(s0, __uint_as_float(v[j]), acc[c + j]);
-                        }
-                        ptx::tcgen05_fence_before_sync();
-                        __syncwarp();
-                        if(lane == 0) ptx::mbar_arrive(dempty_bar(rb.s));
-                        ++seg_units;
-                        const bool seg_end = (i + 1 == n_my) || (kg + 1 == k_units);
-                        if(seg_end) flush();
-                        adv(nt, kg);
-                        r.advance(1, DQ_MD);
-                        rb.advance(1, DQ_DBUF);
-                    }
-                }
-                if(tr) CKB_TR(5, ia, 3);
-                // refill the two ring entries just consumed with the scales of units ia+4, ia+5
-#pragma unroll
-                for(int h = 0; h < 2; ++h)
-                    if(GROUP && ia + h + 4 < n_my) { sc_ring[2 * pr + h] = load_scale(ntp, kgp); adv(ntp, kgp); }
+                unit(i + DQ_TEAMS, nt, kg, scB, zB);
+                adv(nt, kg, DQ_TEAMS);
+                if(GROUP && i + 3 * DQ_TEAMS < n_my) { scB = load_scale2(ntp, kgp); zB = load_zero(ntp, kgp); }
+                adv(ntp, kgp, DQ_TEAMS);
             }
         }
     }
 
     ptx::tcgen05_fence_before_sync();
     __syncthreads();
-    if(warp == DQ_WARP_TMEM)
+    if(warp == DQ_WARP_MMA)
     {
         ptx::tcgen05_fence_after_sync();
-        ptx::tmem_dealloc<TMEM_COLS>(tmem_base);
+        ptx::tmem_dealloc<DQ_TMEM_COLS>(tmem_base);
     }
 }
 
@@ -630,7 +563,16 @@ int dispatch_decode(int wf, bool f16, const WQPlan* wp, const DQArgs& a, const c
     }
 }
 
-int decode_smem(int n_mma, int wf) { return dq_smem_bytes(n_mma, wf); }
+int dispatch_decode_n(int n_mma, int wf, bool f16, const WQPlan* wp, const DQArgs& a, const ckb_gemm_plan& plan,
+                      cudaStream_t st)
+{
+    switch(n_mma)
+    {
+    case 16: return dispatch_decode<16>(wf, f16, wp, a, plan, st);
+    case 32: return dispatch_decode<32>(wf, f16, wp, a, plan, st);
+    default: return dispatch_decode<64>(wf, f16, wp, a, plan, st);
+    }
+}
 
 } // namespace
 
@@ -655,14 +597,16 @@ int plan_wq_decode(const ckb_gemm_problem& p, ckb_gemm_plan& plan)
     wp->units_total    = n_tiles * k_units;
     wp->units_per_tile = k_units;
     const int sms      = device_info().sm_count > 0 ? device_info().sm_count : 148;
-    plan.grid            = std::max(1, std::min(sms, wp->units_total));
+    int per_sm         = dq_smem_bytes(n_mma, wf) <= 113 * 1024 ? 2 : 1;
+    if(const char* e = getenv("CKB_DECODE_CTAS_PER_SM")) per_sm = std::max(1, atoi(e));
+    plan.grid            = std::max(1, std::min(sms * per_sm, wp->units_total));
     plan.block           = DQ_THREADS;
-    plan.smem_bytes      = decode_smem(n_mma, wf);
+    plan.smem_bytes      = dq_smem_bytes(n_mma, wf);
     plan.split_units     = k_units;
     plan.workspace_bytes = uint64_t(n_tiles) * n_mma * DQ_UNIT_N * 4 + uint64_t(n_tiles) * 4;
     static const char* wfn[] = {"w4g128", "w8mul", "w8fpaintb", "w8pass"};
-    snprintf(plan.kernel_name, sizeof plan.kernel_name, "wq_decode_%s_%s_tmemA_streamk_128x%dx128_t%d",
-             wfn[wf], f16 ? "f16" : "bf16", n_mma, DQ_TEAMS);
+    snprintf(plan.kernel_name, sizeof plan.kernel_name, "wq_decode_%s_%s_tmemA_streamk_128x%dx128_t%dx%d",
+             wfn[wf], f16 ? "f16" : "bf16", n_mma, DQ_TEAMS, per_sm);
     return CKB_OK;
 }
 
@@ -685,24 +629,24 @@ int run_wq_decode(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, void* wo
     a.ws          = static_cast<float*>(workspace);
     a.counters    = reinterpret_cast<int*>(static_cast<uint8_t*>(workspace) + size_t(a.n_tiles) * wp->n_mma * DQ_UNIT_N * 4);
     a.idesc       = ptx::make_idesc(1, f16 ? 0 : 1, f16 ? 0 : 1, 128, wp->n_mma);
+    a.trace       = nullptr;
     fill_epi_params(p, a.ep);
-    a.trace = nullptr;
     if(const char* tf = getenv("CKB_TRACE"))
     {
+        // debug only: record block 0's timeline of this launch and dump it as text
         static long long* buf = nullptr;
-        if(!buf) cudaMallocManaged(&buf, 6 * 64 * 4 * sizeof(long long));
+        constexpr int NW = 6 * 64 * 4;
+        if(!buf) cudaMallocManaged(&buf, NW * sizeof(long long));
         cudaDeviceSynchronize();
-        memset(buf, 0, 6 * 64 * 4 * sizeof(long long));
+        memset(buf, 0, NW * sizeof(long long));
         a.trace = buf;
-        int rc = wp->n_mma == 16 ? dispatch_decode<16>(wf, f16, wp, a, plan, stream)
-                                 : (wp->n_mma == 32 ? dispatch_decode<32>(wf, f16, wp, a, plan, stream)
-                                                    : dispatch_decode<64>(wf, f16, wp, a, plan, stream));
+        const int rc = dispatch_decode_n(wp->n_mma, wf, f16, wp, a, plan, stream);
         cudaDeviceSynchronize();
         if(FILE* f = fopen(tf, "w"))
         {
             long long t0 = 0;
-            for(int i = 0; i < 6 * 64 * 4; ++i) if(buf[i] && (!t0 || buf[i] < t0)) t0 = buf[i];
-            const char* names[6] = {"prod", "mma", "dq0", "dq1", "dq2", "epi"};
+            for(int i = 0; i < NW; ++i) if(buf[i] && (!t0 || buf[i] < t0)) t0 = buf[i];
+            const char* names[6] = {"prod", "mma", "dq0", "dq1", "dq2", "dq3"};
             for(int r = 0; r < 6; ++r)
                 for(int i = 0; i < 64; ++i)
                 {
@@ -716,12 +660,7 @@ int run_wq_decode(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, void* wo
         }
         return rc;
     }
-    switch(wp->n_mma)
-    {
-    case 16: return dispatch_decode<16>(wf, f16, wp, a, plan, stream);
-    case 32: return dispatch_decode<32>(wf, f16, wp, a, plan, stream);
-    default: return dispatch_decode<64>(wf, f16, wp, a, plan, stream);
-    }
+    return dispatch_decode_n(wp->n_mma, wf, f16, wp, a, plan, stream);
 }
 
 } // namespace ckb

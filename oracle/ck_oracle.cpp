@@ -186,7 +186,8 @@ int build_b(Ctx& c)
                 v              = f16_to_f32(r);
                 break;
             }
-            case ORC_BOP_GROUP_F32: {
+            case ORC_BOP_GROUP_F32:
+            case ORC_BOP_GROUP_RTN: {
                 // [EXT] K-blocked scales; host pattern of gemm_multiply_multiply_xdl_fp8_ab_scale.cpp:258-290:
                 // pre-scale B into a FLOAT tensor with b1(k / ScaleBlockK, n), then ReferenceGemm<float,...>.
                 if(p.group_size <= 0)
@@ -201,6 +202,8 @@ int build_b(Ctx& c)
                                      : p.zero_const;
                 const float s = load_as_f32(p.s_dtype, p.scale, g * p.s_sk + n * p.s_sn);
                 v             = float(q - z) * s;
+                if(p.b_op == ORC_BOP_GROUP_RTN) // one rounding into A's type (RNE)
+                    v = p.a_dtype == ORC_BF16 ? bf16_to_f32(f32_to_bf16_rtn(v)) : f16_to_f32(f32_to_f16(v));
                 break;
             }
             default: g_err = "unknown b_op"; return -1;

@@ -38,7 +38,10 @@ enum orc_b_op {
     ORC_BOP_PASSTHROUGH = 0, /* b = type_convert<AType>(B0)            unary_element_wise_operation.hpp:112-121 */
     ORC_BOP_MULTIPLY    = 1, /* Multiply<bhalf_t,int8_t,bhalf_t>        binary_element_wise_operation.hpp:184-190 (truncating bf16) */
     ORC_BOP_FPAINTB     = 2, /* type_convert<A>(b) * scale in A's type  reference_fpAintB_gemm.hpp:110 (fp16, one rounding) */
-    ORC_BOP_GROUP_F32   = 3  /* [EXT] float(q - zp[k/g,n]) * float(s[k/g,n]); pattern: gemm_multiply_multiply_xdl_fp8_ab_scale.cpp:258-290 */
+    ORC_BOP_GROUP_F32   = 3, /* [EXT] float(q - zp[k/g,n]) * float(s[k/g,n]); pattern: gemm_multiply_multiply_xdl_fp8_ab_scale.cpp:258-290 */
+    ORC_BOP_GROUP_RTN   = 4  /* [EXT] the same product rounded ONCE (nearest-even) into A's type before the GEMM, as CK's
+                                dequant B-functors do (reference_fpAintB_gemm.hpp:110; bf16 through bf16_convert_rtn,
+                                type_convert.hpp:508-549).  This is the definition the W4A16 kernels implement. */
 };
 
 /* CDE (epilogue) functor */

@@ -15,7 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB_PATH = os.path.join(_HERE, "libck_oracle.so")
 
 F32, F16, BF16, I8, U8, I32 = 0, 1, 2, 3, 4, 5
-BOP_PASSTHROUGH, BOP_MULTIPLY, BOP_FPAINTB, BOP_GROUP_F32 = 0, 1, 2, 3
+BOP_PASSTHROUGH, BOP_MULTIPLY, BOP_FPAINTB, BOP_GROUP_F32, BOP_GROUP_RTN = 0, 1, 2, 3, 4
 (CDE_PASSTHROUGH, CDE_ADD, CDE_FASTGELU, CDE_ADD_FASTGELU, CDE_MULTIPLY, CDE_MULTIPLY_ADD,
  CDE_MULTIPLY_FASTGELU, CDE_MULTIPLY_ADD_FASTGELU, CDE_MULTIPLY_MULTIPLY, CDE_ACT_MUL_CLAMP,
  CDE_ADD_ACT_MUL_CLAMP, CDE_ACT_MUL2_CLAMP, CDE_ADD_ACT_MUL2_CLAMP) = range(13)
