@@ -218,9 +218,12 @@ __device__ __forceinline__ void tcgen05_fence_after_sync()
 {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 }
-__device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads)
+// barrier id is an immediate: a register id makes ptxas reserve all 16 hardware barriers for the CTA,
+// which silently limits residency to one CTA per SM
+template <int ID>
+__device__ __forceinline__ void named_bar_sync(uint32_t nthreads)
 {
-    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+    asm volatile("bar.sync %0, %1;" ::"n"(ID), "r"(nthreads) : "memory");
 }
 
 // ------------------------------------------------------------------ L2 cache policies

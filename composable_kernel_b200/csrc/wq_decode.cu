@@ -117,7 +117,9 @@ static __device__ __noinline__ void decode_drain(const DQArgs& args, int nt, int
     const int kg_first  = (nt == nt0) ? kg0 : 0;
     const int seg_units = kg - kg_first + 1;
     const int k_units   = args.k_units;
+    if(q == 0 && lane == 0) CKB_TR(4, sidx, 0);
     ptx::mbar_wait(dfull0 + 8u * d, (sidx >> 1) & 1);
+    if(q == 0 && lane == 0) CKB_TR(4, sidx, 1);
     ptx::tcgen05_fence_after_sync();
     float acc[N_MMA];
     const uint32_t taddr = tmem_d0 + d * N_MMA + (uint32_t(q * 32) << 16);
@@ -133,41 +135,65 @@ static __device__ __noinline__ void decode_drain(const DQArgs& args, int nt, int
     ptx::tcgen05_fence_before_sync();
     __syncwarp();
     if(lane == 0) ptx::mbar_arrive(dempty0 + 8u * d);
-    const int n    = nt * DQ_UNIT_N + row;
-    const int mmax = min(args.M, N_MMA);
+    const int n = nt * DQ_UNIT_N + row;
+    // common case (PassThrough, 16-bit E, no D tensors): branch-free stores; otherwise the generic functor path
+    const bool fast = ep.cde_op == CKB_CDE_PASSTHROUGH && (ep.e_dtype == CKB_BF16 || ep.e_dtype == CKB_F16);
+    auto emit = [&](const float* v) {
+        if(n >= args.N) return;
+        if(fast)
+        {
+            uint16_t* e = static_cast<uint16_t*>(ep.e) + n;
+#pragma unroll
+            for(int j = 0; j < N_MMA; ++j)
+                if(j < args.M)
+                    e[(long long)j * ep.lde] = ep.e_dtype == CKB_BF16 ? f32_to_bf16_bits(v[j], ep.flags)
+                                                                       : __half_as_ushort(__float2half_rn(v[j]));
+        }
+        else
+        {
+#pragma unroll
+            for(int j = 0; j < N_MMA; ++j)
+                if(j < args.M) store_one(ep, j, n, v[j]);
+        }
+    };
     if(seg_units == k_units)
     {
-        if(n < args.N)
-        {
-#pragma unroll 1
-            for(int j = 0; j < mmax; ++j) store_one(ep, j, n, acc[j]);
-        }
+        emit(acc); // this CTA owned the whole K range of the tile
         return;
     }
-    float* ws = args.ws + ((size_t)nt * N_MMA) * DQ_UNIT_N + row;
-#pragma unroll 1
-    for(int j = 0; j < mmax; ++j) ptx::red_add_f32(ws + j * DQ_UNIT_N, acc[j]);
+    // partial tile: workspace layout [tile][row][N_MMA] so each thread reduces with 128-bit red.add
+    // (rows >= M hold exact zeros: the activation box is zero-filled by TMA)
+    float* ws = args.ws + ((size_t)nt * DQ_UNIT_N + row) * N_MMA;
+#pragma unroll
+    for(int j = 0; j < N_MMA; j += 4) ptx::red_add_v4_f32(ws + j, acc[j], acc[j + 1], acc[j + 2], acc[j + 3]);
+    if(q == 0 && lane == 0) CKB_TR(4, sidx, 2);
     __threadfence();
-    ptx::named_bar_sync(bar_id, 128);
+    if(q == 0 && lane == 0) CKB_TR(4, sidx, 3);
+    if(bar_id == 1) ptx::named_bar_sync<1>(128); else ptx::named_bar_sync<2>(128);
     if(q == 0 && lane == 0)
     {
         const int old = atomicAdd(args.counters + nt, seg_units);
         *flag         = (old + seg_units == k_units) ? 1 : 0;
     }
-    ptx::named_bar_sync(bar_id, 128);
+    if(bar_id == 1) ptx::named_bar_sync<1>(128); else ptx::named_bar_sync<2>(128);
     const int last = *flag;
-    ptx::named_bar_sync(bar_id, 128);
+    if(bar_id == 1) ptx::named_bar_sync<1>(128); else ptx::named_bar_sync<2>(128);
+    if(q == 0 && lane == 0) CKB_TR(4, 32 + sidx, 0);
     if(last)
     {
         __threadfence();
-#pragma unroll 1
-        for(int j = 0; j < mmax; ++j)
-        {
-            const float v = __ldcg(ws + j * DQ_UNIT_N);
-            __stcg(ws + j * DQ_UNIT_N, 0.f);
-            if(n < args.N) store_one(ep, j, n, v);
-        }
+        float4 v4[N_MMA / 4];
+#pragma unroll
+        for(int j = 0; j < N_MMA / 4; ++j) v4[j] = __ldcg(reinterpret_cast<const float4*>(ws) + j);
+#pragma unroll
+        for(int j = 0; j < N_MMA / 4; ++j) __stcg(reinterpret_cast<float4*>(ws) + j, make_float4(0.f, 0.f, 0.f, 0.f));
         if(q == 0 && lane == 0) args.counters[nt] = 0;
+#pragma unroll
+        for(int j = 0; j < N_MMA / 4; ++j)
+        {
+            acc[4 * j] = v4[j].x; acc[4 * j + 1] = v4[j].y; acc[4 * j + 2] = v4[j].z; acc[4 * j + 3] = v4[j].w;
+        }
+        emit(acc);
     }
 }
 
@@ -205,6 +231,7 @@ wq_decode_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constan
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
+    if(threadIdx.x == 0) CKB_TR(5, 0, 0);
 
     if(warp == DQ_WARP_PROD && lane == 0)
     {
@@ -235,6 +262,7 @@ wq_decode_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constan
     uint32_t tmem_base;
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
     ptx::pdl_launch_dependents();
+    if(threadIdx.x == 0) CKB_TR(5, 0, 1);
 
     const long long u_begin = args.total_units * blockIdx.x / gridDim.x;
     const long long u_end   = args.total_units * (blockIdx.x + 1) / gridDim.x;
@@ -276,7 +304,9 @@ wq_decode_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constan
             // programmatic-dependent-launch wait, activations only after it.
             int iw = 0, ia = 0;
             for(; iw < min(WST, n_my); ++iw) issue_w(iw);
+            CKB_TR(0, 0, 0);
             ptx::pdl_wait_prior_grids();
+            CKB_TR(0, 0, 1);
             for(; ia < min(ACT_ST, n_my); ++ia) issue_a(ia);
             Ring rw{0, 0}; // weight slot of unit iw; parity of its previous use's wread phase
             Ring rt{0, 0}; // activation slot of unit ia
@@ -462,7 +492,11 @@ wq_decode_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constan
             __syncwarp();
             if(lane == 0) ptx::mbar_arrive(afull_bar(a_s));
             if(tr) CKB_TR(2 + team, i, 3);
-            if((i + 1 == n_my) || (kg + 1 == k_units)) drain(nt, kg);
+            if((i + 1 == n_my) || (kg + 1 == k_units))
+            {
+                drain(nt, kg);
+                if(tr) CKB_TR(5, 1 + i, team);
+            }
         };
 
         // Group scales / zero points come straight from global memory, two team-iterations ahead, through
@@ -531,7 +565,17 @@ int launch_decode(const WQPlan* wp, const DQArgs& a, const ckb_gemm_plan& plan, 
     if(!attr_set)
     {
         CKB_CUDA_CHECK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        // without this the driver sizes the L1/shared carve-out for ONE block and the second CTA never fits
+        CKB_CUDA_CHECK(cudaFuncSetAttribute(kfn, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                            cudaSharedmemCarveoutMaxShared));
         attr_set = true;
+        if(getenv("CK_LOGGING"))
+        {
+            int nb = 0;
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kfn, DQ_THREADS, smem);
+            fprintf(stderr, "ckb: wq_decode<%d,%d,%d> smem %d B, %d threads, resident CTAs/SM = %d\n", N_MMA, WF, int(F16),
+                    smem, DQ_THREADS, nb);
+        }
     }
     cudaLaunchConfig_t cfg{};
     cfg.gridDim          = dim3(plan.grid);
@@ -634,19 +678,22 @@ int run_wq_decode(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, void* wo
     if(const char* tf = getenv("CKB_TRACE"))
     {
         // debug only: record block 0's timeline of this launch and dump it as text
-        static long long* buf = nullptr;
+        static long long* dbuf = nullptr;
         constexpr int NW = 6 * 64 * 4;
-        if(!buf) cudaMallocManaged(&buf, NW * sizeof(long long));
+        static long long buf[NW];
+        if(!dbuf) cudaMalloc(&dbuf, NW * sizeof(long long));
         cudaDeviceSynchronize();
-        memset(buf, 0, NW * sizeof(long long));
-        a.trace = buf;
+        cudaMemset(dbuf, 0, NW * sizeof(long long));
+        cudaDeviceSynchronize();
+        a.trace = dbuf;
         const int rc = dispatch_decode_n(wp->n_mma, wf, f16, wp, a, plan, stream);
         cudaDeviceSynchronize();
+        cudaMemcpy(buf, dbuf, NW * sizeof(long long), cudaMemcpyDeviceToHost);
         if(FILE* f = fopen(tf, "w"))
         {
             long long t0 = 0;
             for(int i = 0; i < NW; ++i) if(buf[i] && (!t0 || buf[i] < t0)) t0 = buf[i];
-            const char* names[6] = {"prod", "mma", "dq0", "dq1", "dq2", "dq3"};
+            const char* names[6] = {"prod", "mma", "dq0", "dq1", "drain", "misc"};
             for(int r = 0; r < 6; ++r)
                 for(int i = 0; i < 64; ++i)
                 {
