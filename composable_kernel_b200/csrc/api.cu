@@ -33,7 +33,7 @@ uint64_t algo_bytes(const ckb_gemm_problem& p)
     uint64_t b = uint64_t(p.M) * p.K * dtype_bytes(p.a_dtype);
     if(p.b_dtype == CKB_I4) b += uint64_t(p.N) * p.K / 2;
     else b += uint64_t(p.N) * p.K * dtype_bytes(p.b_dtype);
-    if(p.b_op == CKB_BOP_GROUP)
+    if(p.b_op == CKB_BOP_GROUP && p.group_size > 0)
     {
         const uint64_t g = (p.K + p.group_size - 1) / p.group_size;
         b += g * p.N * dtype_bytes(p.s_dtype);
