@@ -243,6 +243,13 @@ int ckb_prepack_b_u8(const void* src, void* dst, int64_t n, void* stream)
     return launch_prepack_u8(src, dst, n, static_cast<cudaStream_t>(stream));
 }
 
+int ckb_prepack_b_rowmajor_i8(const void* src, int64_t ld_src, int32_t K, int32_t N, void* dst, void* stream)
+{
+    if(!src || !dst || K < 0 || N < 0 || ld_src < N) return set_error(CKB_ERR_INVALID, "bad prepack arguments");
+    if(!device_info().ok) return set_error(CKB_ERR_NO_DEVICE, "no sm_100 device");
+    return launch_transpose_i8(src, ld_src, K, N, dst, K, static_cast<cudaStream_t>(stream));
+}
+
 uint64_t ckb_prepack_b_int4_bytes(int32_t N, int32_t K)
 {
     if(N <= 0 || K <= 0) return 0;

@@ -172,6 +172,10 @@ int ckb_gemm_run_host(const ckb_gemm_problem* problem, void* staging, void* work
 /* int8 -> biased uint8 (u8 = int8 + 128), n elements, device pointers. */
 int ckb_prepack_b_u8(const void* src_i8, void* dst_u8, int64_t n, void* stream);
 
+/* Row-major int8 B[k,n] = src[k*ld_src + n] (CK's mk_kn_mn) -> K-major dst[n*K + k], the layout the kernels
+   stream.  One-time weight transform, device pointers. */
+int ckb_prepack_b_rowmajor_i8(const void* src_kn, int64_t ld_src, int32_t K, int32_t N, void* dst_nk, void* stream);
+
 /* [EXT] 4-bit codes, one per byte, logical B[k,n] = src[k*src_sk + n*src_sn] (device) ->
    tile-major packed layout consumed by the W4A16 kernels.  dst needs ckb_prepack_b_int4_bytes(). */
 uint64_t ckb_prepack_b_int4_bytes(int32_t N, int32_t K);
