@@ -290,6 +290,31 @@ def main():
                "note": "ckb_gemm_run_host per GEMM: pinned-host A -> device, kernel, E -> pinned host, stream sync; "
                        "weights stay device-resident (the reference also uploads weights once, outside timing)"}
 
+    # ---- N-sharded path with the output all-gather (NCCL over NVLink), timed separately ----------------
+    with_gather = None
+    if world > 1:
+        from composable_kernel_b200 import shard
+        sel = gemm_ops[::8]  # bounded sample of the step's GEMM list (every 8th launch)
+        def gather_step():
+            s_ = torch.cuda.current_stream().cuda_stream
+            for op in sel:
+                op.run(s_)
+                shard.all_gather_columns(outs[(op.problem.M, op.problem.N)], world, row_major=False)
+        gather_step()
+        barrier()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        for _ in range(3):
+            gather_step()
+        g1.record()
+        barrier()
+        tg = torch.tensor([g0.elapsed_time(g1) / 3], dtype=torch.float64, device=dev)
+        dist.all_reduce(tg, op=dist.ReduceOp.MAX)
+        sel_bytes = sum(algo_bytes(op.problem.M, op.problem.N, op.problem.K) for op in sel)
+        with_gather = {"value": world * sel_bytes / (float(tg.item()) * 1e-3) / 1e9, "unit": "GB/s",
+                       "sample": f"every 8th GEMM of the step ({len(sel)} launches), eager, all_gather_into_tensor of "
+                                 "each E slice into E_all[G][M][N/G] after every GEMM"}
+
     if rank == 0:
         peak, peak_src = peaks()
         us_per_launch = ms_per_step * 1e3 / launches_per_step
@@ -297,6 +322,11 @@ def main():
         cpu = None
         if not args.no_cpu_baseline:
             cpu = cpu_baseline()
+        traffic = None  # dram bytes per launch from the committed ncu --set full capture (ratio x algorithmic bytes)
+        tp = os.path.join(ROOT, "profiles", "r1_traffic.json")
+        if os.path.exists(tp):
+            with open(tp) as f:
+                traffic = json.load(f)["traffic_over_algorithmic"] * step_bytes / launches_per_step
         line = {
             "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
@@ -305,13 +335,16 @@ def main():
                                    "((4096,4096)x4,(11008,4096)x2,(4096,11008)x1)",
                        "launch": "cuda-graph replay" if graph is not None else "eager",
                        "l2": "inputs larger than L2 (3.4 GB of distinct weights per step)",
-                       "parallelism": f"column-shard x{world} (independent shards, no collective)"},
+                       "parallelism": f"column-shard x{world}: every rank owns an N-shard of the shapes above "
+                                      "(independent shards, no collective in the GEMM; all-gather reported in with_allgather)"},
             "tflops": world * step_flops / (ms_per_step * 1e-3) / 1e12,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "frac": achieved / peak, "traffic": traffic, "algorithmic_bytes_per_launch": step_bytes / launches_per_step,
+                         "peak_source": peak_src,
                          "kernel": gemm_ops[0].kernel_name, "us_per_launch": us_per_launch},
             "cpu_baseline": cpu,
             "e2e": e2e,
+            "with_allgather": with_gather,
             "gpu_launches": launches_per_step * args.steps,
             "clocks": clk,
             "detail": detail,

@@ -7,6 +7,7 @@
 #include "ck_oracle.h"
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstring>
 #include <random>
@@ -138,7 +139,9 @@ int build_b(Ctx& c)
         return 0;
     }
     c.bf.resize(size_t(N) * K);
-    for(int n = 0; n < N; ++n)
+    std::atomic<int> rc_all{0};
+    auto do_cols = [&](int n_begin, int n_end) -> void {
+    for(int n = n_begin; n < n_end; ++n)
     {
         for(int k = 0; k < K; ++k)
         {
@@ -164,7 +167,7 @@ int build_b(Ctx& c)
                 if(p.b_dtype != ORC_I8 || p.s_dtype != ORC_BF16 || p.a_dtype != ORC_BF16)
                 {
                     g_err = "Multiply B-op is defined for int8 B0, bf16 B1, bf16 A only";
-                    return -1;
+                    rc_all = -1; return;
                 }
                 const float x0 = float(static_cast<const int8_t*>(p.b)[boff]);
                 const float x1 =
@@ -178,7 +181,7 @@ int build_b(Ctx& c)
                 if(p.b_dtype != ORC_I8 || p.s_dtype != ORC_F16 || p.a_dtype != ORC_F16)
                 {
                     g_err = "fpAintB is defined for fp16 A, int8 B, fp16 scale only";
-                    return -1;
+                    rc_all = -1; return;
                 }
                 const half_t q = static_cast<half_t>(static_cast<const int8_t*>(p.b)[boff]);
                 const half_t s = static_cast<const half_t*>(p.scale)[k * p.s_sk + n * p.s_sn];
@@ -193,7 +196,7 @@ int build_b(Ctx& c)
                 if(p.group_size <= 0)
                 {
                     g_err = "group_size must be > 0";
-                    return -1;
+                    rc_all = -1; return;
                 }
                 const int g = k / p.group_size;
                 int q       = (p.b_dtype == ORC_U8) ? int(static_cast<const uint8_t*>(p.b)[boff])
@@ -206,13 +209,30 @@ int build_b(Ctx& c)
                     v = p.a_dtype == ORC_BF16 ? bf16_to_f32(f32_to_bf16_rtn(v)) : f16_to_f32(f32_to_f16(v));
                 break;
             }
-            default: g_err = "unknown b_op"; return -1;
+            default: rc_all = -1; return;
             }
             c.bf[size_t(n) * K + k] = v;
         }
     }
+    };
+    int nt = p.num_threads > 0 ? p.num_threads : int(std::thread::hardware_concurrency());
+    nt     = std::max(1, std::min(nt, N / 64 + 1));
+    const int per = (N + nt - 1) / nt;
+    std::vector<std::thread> th;
+    for(int t = 0; t < nt; ++t)
+    {
+        const int b = t * per, e = std::min(N, b + per);
+        if(b < e) th.emplace_back(do_cols, b, e);
+    }
+    for(auto& t : th) t.join();
+    if(rc_all != 0)
+    {
+        g_err = "unsupported dtype / b_op combination for the B operand (see ck_oracle.h)";
+        return -1;
+    }
     return 0;
 }
+
 
 // CDE functors on a float C (already rounded through the CShuffle type).
 inline bool cde_float(const orc_problem& p, float c, float d0, float d1, float& e)
