@@ -150,9 +150,16 @@ int ckb_gemm_query(const ckb_gemm_problem* pp, ckb_gemm_plan* plan)
     if(p.lda % 8 || p.lda < p.K) return unsupported(plan, "lda must be a multiple of 8 and >= K");
     if(p.lde < p.N) return unsupported(plan, "lde < N");
     if(!device_info().ok) { plan->supported = 0; return set_error(CKB_ERR_NO_DEVICE, "no sm_100 device"); }
+    if(p.M > 64 && p.K % 8 == 0)
     {
-        // M <= 64: one pass of the decode kernel.  Larger M: the same kernel over 64-row slabs
-        // (interim; the persistent-tile prefill kernel replaces this for M > 64).
+        // prefill-shaped: expand the weight once, then the dense tcgen05 GEMM with the fused epilogue
+        if(int rc = plan_wq_prefill(p, *plan)) return rc;
+        plan->kernel_id = KID_WQ_PREFILL;
+        plan->supported = 1;
+        return CKB_OK;
+    }
+    {
+        // M <= 64: one pass of the stream-K decode kernel (larger M with K % 8 != 0: 64-row slabs of it)
         ckb_gemm_problem q = p;
         q.M = std::min(p.M, 64);
         if(int rc = plan_wq_decode(q, *plan)) { if(rc == CKB_ERR_UNSUPPORTED) { plan->supported = 0; return CKB_OK; } return rc; }
@@ -172,6 +179,7 @@ int ckb_gemm_run(const ckb_gemm_problem* pp, const ckb_gemm_plan* plan, void* wo
     switch(plan->kernel_id)
     {
     case KID_GEMM_SS: return run_gemm_ss(*pp, *plan, st);
+    case KID_WQ_PREFILL: return run_wq_prefill(*pp, *plan, workspace, st);
     case KID_WQ_DECODE: {
         if(pp->M <= 64) return run_wq_decode(*pp, *plan, workspace, st);
         // slabs of 64 rows; each slab needs its own activation tensor map

@@ -245,3 +245,51 @@ def test_host_buffer_entry_point_matches_device_path():
     capi.check(capi.lib().ckb_gemm_run_host(C.byref(p), staging.data_ptr(), op.workspace.data_ptr(),
                                             torch.cuda.current_stream().cuda_stream))
     assert np.array_equal(he.numpy().view(np.uint16), ref)
+
+
+# ------------------------------------------------------------------------------------------ prefill-shaped (M > 64)
+@pytest.mark.parametrize("M,N,K", [(256, 512, 1024), (130, 384, 392), (1024, 256, 128)])
+def test_prefill_w8a16_and_w4a16_vs_oracle(M, N, K):
+    o = orc()
+    rng = np.random.default_rng(M + N)
+    a = rand_bf16(rng, (M, K))
+    qn = rng.integers(-128, 128, (N, K + (-K) % 16)).astype(np.int8)[:, :K]   # ldb padded to 16
+    s = o.bf16_trunc((rng.random(N) * 0.02 + 0.001).astype(np.float32))
+    bias = rand_bf16(rng, (N,))
+    import torch
+    from composable_kernel_b200 import capi, ops
+    e = torch.zeros(M, N, dtype=torch.bfloat16, device="cuda")
+    bd = H.to_dev(np.ascontiguousarray(np.pad(qn, ((0, 0), (0, (-K) % 16)))))[:, :K]
+    op = ops.GemmOp(H.to_dev(a, True), bd, e, b_op=capi.BOP_MULTIPLY, scale=H.to_dev(s, True), ds=(H.to_dev(bias, True),),
+                    d_strides=((0, 1),), cde_op=capi.CDE_ADD)
+    assert op.supported and "prefill" in op.kernel_name, (op.why, op.kernel_name)
+    op.run()
+    torch.cuda.synchronize()
+    ref = o.gemm(a, o.BF16, qn.T, o.I8, o.BF16, b_op=o.BOP_MULTIPLY, scale=np.broadcast_to(s, (K, N)), s_dtype=o.BF16,
+                 ds=(np.broadcast_to(bias, (M, N)),), d_dtypes=(o.BF16,), cde_op=o.CDE_ADD)
+    bad, err = H.bf16_close(H.from_dev_bf16(e), ref, RTOL, ATOL)
+    assert bad == 0, f"w8 max err {err}"
+    if K % 128 == 0:
+        q = rng.integers(0, 16, (K, N)).astype(np.uint8)
+        sg = o.bf16_trunc((rng.random((K // 128, N)) * 0.015 + 0.005).astype(np.float32))
+        z = rng.integers(0, 16, (K // 128, N)).astype(np.uint8)
+        got, op4 = H.run_w4a16(a, q, sg, z)
+        assert "prefill" in op4.kernel_name
+        ref4 = o.gemm(a, o.BF16, q, o.U8, o.BF16, b_op=o.BOP_GROUP_RTN, scale=sg, s_dtype=o.BF16, zero=z, group_size=128)
+        bad, err = H.bf16_close(got, ref4, RTOL, ATOL)
+        assert bad == 0, f"w4 max err {err}"
+
+
+def test_prefill_fpaintb_cfg1_row_sample():
+    """cfg1 class (example 64 default shape family) on a row sample against the oracle."""
+    o = orc()
+    rng = np.random.default_rng(64)
+    M, N, K = 384, 512, 1024
+    a = rng.standard_normal((M, K)).astype(np.float16)
+    qn = rng.integers(-128, 128, (N, K)).astype(np.int8)
+    s = (rng.random(N) * 0.02 + 0.001).astype(np.float16)
+    got, op = H.run_fpaintb(a, qn, s)
+    assert "prefill" in op.kernel_name
+    ref = o.gemm(a, o.F16, qn.T, o.I8, o.F16, b_op=o.BOP_FPAINTB, scale=np.broadcast_to(s, (K, N)), s_dtype=o.F16)
+    bad, err = H.f_close(got, ref, RTOL, ATOL)
+    assert bad == 0, f"max err {err}"
