@@ -266,7 +266,7 @@ def main():
             C.memmove(C.byref(p), C.byref(op.problem), C.sizeof(p))
             p.a = host_a[(p.M, p.K)].data_ptr()
             p.e = host_e[(p.M, p.N)].data_ptr()
-            probs.append((p, op.workspace.data_ptr()))
+            probs.append((p, op.workspace.data_ptr() if op.workspace is not None else None))
             h2d += 2 * p.M * p.K
             d2h += 2 * p.M * p.N
         s = torch.cuda.current_stream().cuda_stream

@@ -11,7 +11,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libckb.so")
+# CKB_LIB selects a debug build of the same library (e.g. lib/libckb_trace.so); never a different implementation
+LIB_PATH = os.environ.get("CKB_LIB") or os.path.join(_HERE, "lib", "libckb.so")
 
 # enums (include/ckb.h)
 F32, F16, BF16, I8, U8, I32, I4 = range(7)
@@ -49,7 +50,7 @@ class GemmPlan(C.Structure):
         ("grid", C.c_int32), ("block", C.c_int32), ("smem_bytes", C.c_int32), ("split_units", C.c_int32),
         ("algo_bytes", C.c_uint64), ("flops", C.c_uint64),
         ("_pad", C.c_ubyte * 48),            # opaque is 64-byte aligned in C
-        ("opaque", C.c_ubyte * 640),
+        ("opaque", C.c_ubyte * 1280),
     ]
 
 

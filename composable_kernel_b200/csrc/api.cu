@@ -128,6 +128,7 @@ int ckb_gemm_query(const ckb_gemm_problem* pp, ckb_gemm_plan* plan)
         if(!p.scale || p.s_dtype != p.a_dtype) return unsupported(plan, "group scales must have A's type");
         if(p.N % 8 || (p.zero && p.N % 16)) return unsupported(plan, "N must be a multiple of 8 (16 with zero points)");
         if(p.zero_const < 0 || p.zero_const > 15) return unsupported(plan, "zero_const out of range");
+        if(p.K % 64) return unsupported(plan, "pre-packed int4 B needs K to be a multiple of 64");
         break;
     case CKB_BOP_MULTIPLY:
         if(p.a_dtype != CKB_BF16 || p.b_dtype != CKB_I8 || p.s_dtype != CKB_BF16 || !p.scale)
@@ -158,6 +159,16 @@ int ckb_gemm_query(const ckb_gemm_problem* pp, ckb_gemm_plan* plan)
         plan->supported = 1;
         return CKB_OK;
     }
+    if(p.b_op == CKB_BOP_GROUP)
+    {
+        // W4A16, M <= 64 (larger M with K % 8 != 0: 64-row slabs): N-split HMMA kernel, no workspace
+        ckb_gemm_problem q = p;
+        q.M = std::min(p.M, 64);
+        if(int rc = plan_wq_gemv(q, *plan)) { if(rc == CKB_ERR_UNSUPPORTED) { plan->supported = 0; return CKB_OK; } return rc; }
+        plan->kernel_id = KID_WQ_GEMV;
+        plan->supported = 1;
+        return CKB_OK;
+    }
     {
         // M <= 64: one pass of the stream-K decode kernel (larger M with K % 8 != 0: 64-row slabs of it)
         ckb_gemm_problem q = p;
@@ -180,8 +191,10 @@ int ckb_gemm_run(const ckb_gemm_problem* pp, const ckb_gemm_plan* plan, void* wo
     {
     case KID_GEMM_SS: return run_gemm_ss(*pp, *plan, st);
     case KID_WQ_PREFILL: return run_wq_prefill(*pp, *plan, workspace, st);
+    case KID_WQ_GEMV:
     case KID_WQ_DECODE: {
-        if(pp->M <= 64) return run_wq_decode(*pp, *plan, workspace, st);
+        const bool gemv = plan->kernel_id == KID_WQ_GEMV;
+        if(pp->M <= 64) return gemv ? run_wq_gemv(*pp, *plan, st) : run_wq_decode(*pp, *plan, workspace, st);
         // slabs of 64 rows; each slab needs its own activation tensor map
         for(int m0 = 0; m0 < pp->M; m0 += 64)
         {
@@ -193,9 +206,9 @@ int ckb_gemm_run(const ckb_gemm_problem* pp, const ckb_gemm_plan* plan, void* wo
                 q.d[i] = static_cast<const uint8_t*>(pp->d[i]) + size_t(m0) * pp->d_sm[i] * dtype_bytes(pp->d_dtype[i]);
             ckb_gemm_plan sub;
             memset(&sub, 0, sizeof sub);
-            if(int rc = plan_wq_decode(q, sub)) return rc;
+            if(int rc = gemv ? plan_wq_gemv(q, sub) : plan_wq_decode(q, sub)) return rc;
             sub.supported = 1;
-            if(int rc = run_wq_decode(q, sub, workspace, st)) return rc;
+            if(int rc = gemv ? run_wq_gemv(q, sub, st) : run_wq_decode(q, sub, workspace, st)) return rc;
         }
         return CKB_OK;
     }
@@ -261,7 +274,7 @@ int ckb_prepack_b_rowmajor_i8(const void* src, int64_t ld_src, int32_t K, int32_
 uint64_t ckb_prepack_b_int4_bytes(int32_t N, int32_t K)
 {
     if(N <= 0 || K <= 0) return 0;
-    return uint64_t((N + 127) / 128) * ((K + 127) / 128) * 8192;
+    return uint64_t((N + 15) / 16) * ((K + 63) / 64) * 512; // [n16 group][k64 block][32 lanes][16 B]
 }
 
 int ckb_prepack_b_int4(const void* src, int64_t sk, int64_t sn, int32_t N, int32_t K, void* dst, void* stream)

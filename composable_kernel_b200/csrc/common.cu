@@ -93,4 +93,25 @@ int encode_tmap_2d(CUtensorMap* out, CUtensorMapDataType dt, int elem_bytes, con
     return CKB_OK;
 }
 
+int encode_tmap_nd(CUtensorMap* out, CUtensorMapDataType dt, int rank, const void* base, const uint64_t* dims,
+                   const uint64_t* strides_bytes, const uint32_t* box, CUtensorMapSwizzle swz)
+{
+    EncodeTiledFn fn = get_encode_fn();
+    if(!fn) return set_error(CKB_ERR_NO_DEVICE, "cuTensorMapEncodeTiled entry point unavailable");
+    if((reinterpret_cast<uintptr_t>(base) & 15) != 0)
+        return set_error(CKB_ERR_UNSUPPORTED, "TMA base pointer must be 16-byte aligned");
+    cuuint64_t gdim[5], gstride[4];
+    cuuint32_t bx[5], estr[5];
+    for(int i = 0; i < rank; ++i) { gdim[i] = dims[i]; bx[i] = box[i]; estr[i] = 1; }
+    for(int i = 0; i + 1 < rank; ++i)
+    {
+        if(strides_bytes[i] % 16 != 0) return set_error(CKB_ERR_UNSUPPORTED, "TMA stride must be a multiple of 16 bytes");
+        gstride[i] = strides_bytes[i];
+    }
+    CUresult r = fn(out, dt, rank, const_cast<void*>(base), gdim, gstride, bx, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if(r != CUDA_SUCCESS) return set_error(CKB_ERR_CUDA, "cuTensorMapEncodeTiled (rank %d) failed with CUresult %d", rank, int(r));
+    return CKB_OK;
+}
+
 } // namespace ckb

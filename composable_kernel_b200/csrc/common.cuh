@@ -41,6 +41,10 @@ int encode_tmap_2d(CUtensorMap* out, CUtensorMapDataType dt, int elem_bytes, con
                    uint64_t rows, uint64_t cols, uint64_t ld_elems, uint32_t box_rows,
                    uint32_t box_cols, CUtensorMapSwizzle swz);
 
+// general tiled map: dims/box innermost first, strides in bytes for dims 1..rank-1
+int encode_tmap_nd(CUtensorMap* out, CUtensorMapDataType dt, int rank, const void* base, const uint64_t* dims,
+                   const uint64_t* strides_bytes, const uint32_t* box, CUtensorMapSwizzle swz);
+
 inline int dtype_bytes(int dt)
 {
     switch(dt)

@@ -91,6 +91,23 @@ __device__ __forceinline__ void dequant_w4_word_scaled(uint32_t w, uint32_t zmag
     }
 }
 
+// Fragment-major W4 word (ckb_prepack_b_int4): pairs 0,2 belong to row r_lo, pairs 1,3 to row r_hi = r_lo + 8, each row with
+// its own (magic + zero point) and scale.  out4 = {(lo;k0,k1), (hi;k0,k1), (lo;k2,k3), (hi;k2,k3)} = m16n8k16 A fragment.
+template <bool F16>
+__device__ __forceinline__ void dequant_w4_word_scaled2(uint32_t w, uint32_t zm_lo, uint32_t zm_hi, uint32_t sc_lo,
+                                                        uint32_t sc_hi, uint32_t* out4)
+{
+    constexpr uint32_t MAGIC = F16 ? 0x64006400u : 0x43004300u;
+#pragma unroll
+    for(int i = 0; i < 4; ++i)
+    {
+        const uint32_t t  = lop3<0xEA>(w >> (4 * i), 0x000F000Fu, MAGIC);
+        const uint32_t zm = (i & 1) ? zm_hi : zm_lo;
+        const uint32_t sc = (i & 1) ? sc_hi : sc_lo;
+        out4[i] = F16 ? hmul2_f16(hsub2_f16(t, zm), sc) : hmul2_bf16(hsub2_bf16(t, zm), sc);
+    }
+}
+
 // ---- W8 fpAintB (fp16): u8 -> 0x6400|u8 = 1024 + u8; minus 1152 (= 0x6480) removes the +128 bias
 // (the reference's own trick, unary_element_wise_operation.hpp:1061-1091); times scale: ONE rounding.
 __device__ __forceinline__ void dequant_u8x4_fpaintb(uint32_t w, uint32_t scale2, uint32_t* out2)

@@ -16,7 +16,8 @@ enum KernelId : int32_t {
     KID_NONE       = 0,
     KID_GEMM_SS    = 1, // K3: TMA + tcgen05 SS (int8 x int8 -> s32, bf16/f16 dense)
     KID_WQ_DECODE  = 2, // K2: weight-dequant -> TMEM A operand, stream-K, M <= 64
-    KID_WQ_PREFILL = 3  // K1: weight-dequant -> TMEM A operand, persistent tiles
+    KID_WQ_PREFILL = 3, // K1: weight dequant pass + dense tcgen05 SS GEMM
+    KID_WQ_GEMV    = 4  // K2 (W4A16): N-split HMMA kernel for M <= 64, no cross-CTA reduction
 };
 
 // ---- K3 ---------------------------------------------------------------------------------------
@@ -37,6 +38,8 @@ struct WQPlan
 };
 int plan_wq_decode(const ckb_gemm_problem& p, ckb_gemm_plan& plan);
 int run_wq_decode(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, void* workspace, cudaStream_t stream);
+int plan_wq_gemv(const ckb_gemm_problem& p, ckb_gemm_plan& plan);
+int run_wq_gemv(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStream_t stream);
 int plan_wq_prefill(const ckb_gemm_problem& p, ckb_gemm_plan& plan);
 int run_wq_prefill(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, void* workspace, cudaStream_t stream);
 

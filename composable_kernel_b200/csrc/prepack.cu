@@ -21,36 +21,39 @@ __global__ void prepack_u8_kernel(const uint8_t* __restrict__ src, uint8_t* __re
         dst[i] = src[i] ^ 0x80;
 }
 
-// [EXT] 4-bit codes (one per byte, logical B[k,n]) -> tile-major packed layout of the W4A16 kernels:
-//   tile (nt, kt) of 128 channels x 128 k = 8192 bytes at ((nt * k_tiles) + kt) * 8192
-//   inside:  [chunk j = 0..3][row r = 0..127][word i = 0..3]  (a warp reads 32 rows x 16 B = 512 B contiguous)
-//   word (j,r,i) holds k = 32 j + 8 i + {0..7} of channel r with nibbles ordered
-//   [k0,k2,k4,k6,k1,k3,k5,k7] so that (w >> 4p) & 0x000F000F yields the pair (k_2p, k_2p+1).
+// [EXT] 4-bit codes (one per byte, logical B[k,n]) -> fragment-major packed layout of the W4A16 kernels:
+//   [n16 group ng][k64 block kb][lane = 4 g + t][word s = 0..3]   (512 B per (ng, kb); a warp reads it with one LDS.128)
+//   word (ng, kb, lane, s) is the mma.sync m16n8k16 A fragment of rows r_lo = 16 ng + g, r_hi = r_lo + 8 and the four
+//   k values k_i = 64 kb + 16 t + 4 s + i (the kernel pairs them with the same k of the activations):
+//     nibble 0 = (r_lo,k0)  4 = (r_lo,k1)  1 = (r_hi,k0)  5 = (r_hi,k1)  2 = (r_lo,k2)  6 = (r_lo,k3)  3 = (r_hi,k2)  7 = (r_hi,k3)
+//   so that (w >> 4p) & 0x000F000F, p = 0..3, yields the fragment registers {a0a1, a2a3, a4a5, a6a7}.
+//   Codes outside N x K are 0 (their activations are zero-filled by TMA).
 __global__ void prepack_int4_kernel(const uint8_t* __restrict__ src, long long sk, long long sn, int N, int K,
-                                    int k_tiles, long long total_words, uint32_t* __restrict__ dst)
+                                    int k_blocks, long long total_words, uint32_t* __restrict__ dst)
 {
     const long long stride = (long long)gridDim.x * blockDim.x;
     for(long long w = (long long)blockIdx.x * blockDim.x + threadIdx.x; w < total_words; w += stride)
     {
-        const int i        = int(w & 3);
-        const int r        = int((w >> 2) & 127);
-        const int j        = int((w >> 9) & 3);
-        const long long t  = w >> 11;
-        const int kt       = int(t % k_tiles);
-        const int nt       = int(t / k_tiles);
-        const int n        = nt * 128 + r;
-        const int k0       = kt * 128 + 32 * j + 8 * i;
-        uint32_t word      = 0;
-        if(n < N)
-        {
-            const int pos[8] = {0, 4, 1, 5, 2, 6, 3, 7}; // nibble position of k0..k7
-#pragma unroll
-            for(int e = 0; e < 8; ++e)
-            {
-                const int k = k0 + e;
-                if(k < K) word |= uint32_t(src[k * sk + n * sn] & 0xF) << (4 * pos[e]);
-            }
-        }
+        const int s        = int(w & 3);
+        const int lane     = int((w >> 2) & 31);
+        const long long bl = w >> 7;
+        const int kb       = int(bl % k_blocks);
+        const int ng       = int(bl / k_blocks);
+        const int g = lane >> 2, t = lane & 3;
+        const int k0       = 64 * kb + 16 * t + 4 * s;
+        const int r_lo = 16 * ng + g, r_hi = r_lo + 8;
+        auto code = [&](int r, int k) -> uint32_t {
+            return (r < N && k < K) ? uint32_t(src[k * sk + r * sn] & 0xF) : 0u;
+        };
+        uint32_t word = 0;
+        word |= code(r_lo, k0 + 0) << 0;
+        word |= code(r_lo, k0 + 1) << 16;
+        word |= code(r_hi, k0 + 0) << 4;
+        word |= code(r_hi, k0 + 1) << 20;
+        word |= code(r_lo, k0 + 2) << 8;
+        word |= code(r_lo, k0 + 3) << 24;
+        word |= code(r_hi, k0 + 2) << 12;
+        word |= code(r_hi, k0 + 3) << 28;
         dst[w] = word;
     }
 }
@@ -86,11 +89,11 @@ int launch_prepack_u8(const void* src, void* dst, long long n, cudaStream_t stre
 
 int launch_prepack_int4(const void* src, long long sk, long long sn, int N, int K, void* dst, cudaStream_t stream)
 {
-    const int n_tiles = (N + 127) / 128, k_tiles = (K + 127) / 128;
-    const long long words = (long long)n_tiles * k_tiles * 2048;
+    const int n_groups = (N + 15) / 16, k_blocks = (K + 63) / 64;
+    const long long words = (long long)n_groups * k_blocks * 128;
     if(words == 0) return CKB_OK;
     const int blocks = int(std::min<long long>((words + 255) / 256, 148 * 16));
-    prepack_int4_kernel<<<blocks, 256, 0, stream>>>(static_cast<const uint8_t*>(src), sk, sn, N, K, k_tiles, words,
+    prepack_int4_kernel<<<blocks, 256, 0, stream>>>(static_cast<const uint8_t*>(src), sk, sn, N, K, k_blocks, words,
                                                     static_cast<uint32_t*>(dst));
     CKB_CUDA_CHECK(cudaGetLastError());
     return CKB_OK;

@@ -263,6 +263,24 @@ __device__ __forceinline__ void tma_load_2d_hint(
                  "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(x), "r"(y), "l"(policy)
                  : "memory");
 }
+// 3-D tiled load global -> smem with an L2 cache hint
+__device__ __forceinline__ void tma_load_3d_hint(
+    uint32_t smem_dst, const CUtensorMap* m, uint32_t bar, int32_t x, int32_t y, int32_t z, uint64_t policy)
+{
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes"
+                 ".L2::cache_hint [%0], [%1, {%3, %4, %5}], [%2], %6;" ::"r"(smem_dst),
+                 "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(x), "r"(y), "r"(z), "l"(policy)
+                 : "memory");
+}
+__device__ __forceinline__ void
+tma_load_3d(uint32_t smem_dst, const CUtensorMap* m, uint32_t bar, int32_t x, int32_t y, int32_t z)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes "
+        "[%0], [%1, {%3, %4, %5}], [%2];" ::"r"(smem_dst),
+        "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(x), "r"(y), "r"(z)
+        : "memory");
+}
 // 2-D tiled store smem -> global (bulk_group completion)
 __device__ __forceinline__ void
 tma_store_2d(const CUtensorMap* m, uint32_t smem_src, int32_t x, int32_t y)
@@ -294,6 +312,39 @@ bulk_load_1d(uint32_t smem_dst, const void* gsrc, uint32_t bytes, uint32_t bar, 
                  "[%0], [%1], %2, [%3], %4;" ::"r"(smem_dst),
                  "l"(reinterpret_cast<uint64_t>(gsrc)), "r"(bytes), "r"(bar), "l"(policy)
                  : "memory");
+}
+
+// ------------------------------------------------------------------ warp-level MMA (HMMA) + shared loads
+// D[16x8] += A[16x16] * B[16x8], 16-bit operands, fp32 accumulate
+template <bool F16>
+__device__ __forceinline__ void mma_m16n8k16(float* d, const uint32_t* a, uint32_t b0, uint32_t b1)
+{
+    if(F16)
+        asm("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                     : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                     : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+    else
+        asm("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                     : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                     : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr)
+{
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ uint32_t lds_u16(uint32_t addr)
+{
+    uint16_t v;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ uint32_t lds_u8(uint32_t addr)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
 }
 
 // ------------------------------------------------------------------ TMEM

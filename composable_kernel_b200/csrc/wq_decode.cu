@@ -30,6 +30,8 @@
 #include "kernels.h"
 #include "ptx.cuh"
 
+#include <vector>
+
 namespace ckb {
 namespace {
 
@@ -55,6 +57,7 @@ struct DQArgs
     int* counters;           // [n_tiles], zero on entry and on exit
     uint32_t idesc;
     long long* trace;        // debug timeline (CKB_TRACE), null in production
+    long long* gtrace;       // debug: per-CTA globaltimer stamps (CKB_GTRACE), null in production
     EpiParams ep;
 };
 
@@ -85,8 +88,13 @@ static __device__ __noinline__ void store_one(const EpiParams& ep, int m, int n,
     do {                                                                                                  \
         if(args.trace && blockIdx.x == 0 && (i) < 64) args.trace[((r)*64 + (i)) * 4 + (k)] = clock64();   \
     } while(0)
+#define CKB_GT(k)                                                                                         \
+    do {                                                                                                  \
+        if(args.gtrace) args.gtrace[blockIdx.x * 8 + (k)] = (long long)ptx::global_timer_ns();            \
+    } while(0)
 #else
 #define CKB_TR(r, i, k) do { } while(0)
+#define CKB_GT(k) do { } while(0)
 #endif
 
 // ring position helper: advance by `step` without integer division
@@ -120,6 +128,7 @@ static __device__ __noinline__ void decode_drain(const DQArgs& args, int nt, int
     if(q == 0 && lane == 0) CKB_TR(4, sidx, 0);
     ptx::mbar_wait(dfull0 + 8u * d, (sidx >> 1) & 1);
     if(q == 0 && lane == 0) CKB_TR(4, sidx, 1);
+    if(q == 0 && lane == 0) CKB_GT(6);
     ptx::tcgen05_fence_after_sync();
     float acc[N_MMA];
     const uint32_t taddr = tmem_d0 + d * N_MMA + (uint32_t(q * 32) << 16);
@@ -232,6 +241,7 @@ wq_decode_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constan
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     if(threadIdx.x == 0) CKB_TR(5, 0, 0);
+    if(threadIdx.x == 0) CKB_GT(0);
 
     if(warp == DQ_WARP_PROD && lane == 0)
     {
@@ -263,6 +273,7 @@ wq_decode_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constan
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
     ptx::pdl_launch_dependents();
     if(threadIdx.x == 0) CKB_TR(5, 0, 1);
+    if(threadIdx.x == 0) CKB_GT(1);
 
     const long long u_begin = args.total_units * blockIdx.x / gridDim.x;
     const long long u_end   = args.total_units * (blockIdx.x + 1) / gridDim.x;
@@ -307,6 +318,7 @@ wq_decode_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constan
             CKB_TR(0, 0, 0);
             ptx::pdl_wait_prior_grids();
             CKB_TR(0, 0, 1);
+            CKB_GT(2);
             for(; ia < min(ACT_ST, n_my); ++ia) issue_a(ia);
             Ring rw{0, 0}; // weight slot of unit iw; parity of its previous use's wread phase
             Ring rt{0, 0}; // activation slot of unit ia
@@ -431,6 +443,8 @@ wq_decode_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constan
             if(tr) CKB_TR(2 + team, i, 0);
             ptx::mbar_wait(wfull_bar(ws_slot), ws_ph);
             if(tr) CKB_TR(2 + team, i, 1);
+            if(tr && i == 0) CKB_GT(3);
+            if(tr && i + DQ_TEAMS >= n_my) CKB_GT(4 + team);
             const uint8_t* st    = smem + ACT_ST * ACT_BYTES + ws_slot * W_BYTES;
             const uint32_t taddr = tmem_base + a_s * 64 + (uint32_t(q * 32) << 16);
             if(GROUP)
@@ -531,6 +545,7 @@ wq_decode_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constan
 
     ptx::tcgen05_fence_before_sync();
     __syncthreads();
+    if(threadIdx.x == 0) CKB_GT(7);
     if(warp == DQ_WARP_MMA)
     {
         ptx::tcgen05_fence_after_sync();
@@ -674,7 +689,37 @@ int run_wq_decode(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, void* wo
     a.counters    = reinterpret_cast<int*>(static_cast<uint8_t*>(workspace) + size_t(a.n_tiles) * wp->n_mma * DQ_UNIT_N * 4);
     a.idesc       = ptx::make_idesc(1, f16 ? 0 : 1, f16 ? 0 : 1, 128, wp->n_mma);
     a.trace       = nullptr;
+    a.gtrace      = nullptr;
     fill_epi_params(p, a.ep);
+    if(const char* gf = getenv("CKB_GTRACE"))
+    {
+        // debug only: per-CTA globaltimer stamps of this launch, dumped as text (one line per CTA)
+        static long long* gbuf = nullptr;
+        const int NW = 8 * 1024;
+        if(!gbuf) cudaMalloc(&gbuf, NW * sizeof(long long));
+        cudaDeviceSynchronize();
+        cudaMemset(gbuf, 0, NW * sizeof(long long));
+        cudaDeviceSynchronize();
+        a.gtrace = gbuf;
+        const int rc = dispatch_decode_n(wp->n_mma, wf, f16, wp, a, plan, stream);
+        cudaDeviceSynchronize();
+        std::vector<long long> hb(NW);
+        cudaMemcpy(hb.data(), gbuf, NW * sizeof(long long), cudaMemcpyDeviceToHost);
+        if(FILE* f = fopen(gf, "a"))
+        {
+            long long t0 = 0;
+            for(int i = 0; i < NW; ++i) if(hb[i] && (!t0 || hb[i] < t0)) t0 = hb[i];
+            fprintf(f, "# M%d N%d K%d grid %d\n", p.M, p.N, p.K, plan.grid);
+            for(int b = 0; b < plan.grid && b < 1024; ++b)
+            {
+                fprintf(f, "%d", b);
+                for(int k = 0; k < 8; ++k) fprintf(f, " %lld", hb[b * 8 + k] ? hb[b * 8 + k] - t0 : -1);
+                fprintf(f, "\n");
+            }
+            fclose(f);
+        }
+        return rc;
+    }
     if(const char* tf = getenv("CKB_TRACE"))
     {
         // debug only: record block 0's timeline of this launch and dump it as text

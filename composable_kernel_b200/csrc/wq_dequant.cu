@@ -51,39 +51,58 @@ wq_dequant_w8_kernel(const uint8_t* __restrict__ b, long long ldb, const uint16_
     }
 }
 
-// pre-packed int4: one thread = one 16-byte chunk = 32 k of one channel (layout of ckb_prepack_b_int4)
+// pre-packed int4 (layout of ckb_prepack_b_int4: [n16 group][k64 block][lane][4 words]): one thread = one 16-byte
+// chunk = 16 consecutive k of channels r_lo and r_hi = r_lo + 8
 template <bool F16>
 __global__ void __launch_bounds__(256)
 wq_dequant_w4_kernel(const uint8_t* __restrict__ packed, const uint16_t* __restrict__ scale, const uint8_t* __restrict__ zero,
-                     int zero_const, int N, int K, int k_tiles, long long total_chunks, uint16_t* __restrict__ out)
+                     int zero_const, int N, int K, int k_blocks, long long total_chunks, uint16_t* __restrict__ out)
 {
-    for(long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total_chunks; t += (long long)gridDim.x * blockDim.x)
+    for(long long c = (long long)blockIdx.x * blockDim.x + threadIdx.x; c < total_chunks; c += (long long)gridDim.x * blockDim.x)
     {
-        const int r        = int(t & 127);
-        const int j        = int((t >> 7) & 3);
-        const long long tl = t >> 9;
-        const int kt = int(tl % k_tiles), nt = int(tl / k_tiles);
-        const int n = nt * 128 + r, k0 = kt * 128 + j * 32;
-        if(n >= N || k0 >= K) continue;
-        const uint4 c     = *reinterpret_cast<const uint4*>(packed + t * 16);
-        const uint32_t sb = scale[(long long)kt * N + n];
-        const uint32_t s2 = sb | (sb << 16);
-        const int z       = zero ? int(zero[(long long)kt * N + n]) : zero_const;
-        const uint32_t zm = F16 ? (0x6400u + z) * 0x10001u : (0x4300u + z) * 0x10001u;
-        uint32_t o[16];
-        dequant_w4_word_scaled<F16>(c.x, zm, s2, o + 0);
-        dequant_w4_word_scaled<F16>(c.y, zm, s2, o + 4);
-        dequant_w4_word_scaled<F16>(c.z, zm, s2, o + 8);
-        dequant_w4_word_scaled<F16>(c.w, zm, s2, o + 12);
-        uint16_t* dst = out + (long long)n * K + k0;
-        if(k0 + 32 <= K && (K % 8) == 0)
-        {
+        const int lane     = int(c & 31);
+        const long long bl = c >> 5;
+        const int kb = int(bl % k_blocks), ng = int(bl / k_blocks);
+        const int g = lane >> 2, t = lane & 3;
+        const int r_lo = 16 * ng + g, r_hi = r_lo + 8;
+        const int k0 = 64 * kb + 16 * t;
+        if(r_lo >= N || k0 >= K) continue;
+        const uint4 v        = *reinterpret_cast<const uint4*>(packed + c * 16);
+        const long long srow = (long long)(kb >> 1) * N;
+        const bool hi_ok     = r_hi < N;
+        const uint32_t sl = scale[srow + r_lo], sh = hi_ok ? scale[srow + r_hi] : 0;
+        const int zl = zero ? int(zero[srow + r_lo]) : zero_const;
+        const int zh = (zero && hi_ok) ? int(zero[srow + r_hi]) : zero_const;
+        const uint32_t magic = F16 ? 0x6400u : 0x4300u;
+        const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+        uint32_t lo[8], hi[8]; // 16 k of each row as packed pairs
 #pragma unroll
-            for(int i = 0; i < 4; ++i) reinterpret_cast<uint4*>(dst)[i] = make_uint4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
+        for(int s = 0; s < 4; ++s)
+        {
+            uint32_t o[4];
+            dequant_w4_word_scaled2<F16>(w4[s], (magic + zl) * 0x10001u, (magic + zh) * 0x10001u, sl | (sl << 16), sh | (sh << 16), o);
+            lo[2 * s] = o[0]; lo[2 * s + 1] = o[2];
+            hi[2 * s] = o[1]; hi[2 * s + 1] = o[3];
+        }
+        uint16_t* dlo = out + (long long)r_lo * K + k0;
+        uint16_t* dhi = out + (long long)r_hi * K + k0;
+        if(k0 + 16 <= K && (K % 8) == 0)
+        {
+            reinterpret_cast<uint4*>(dlo)[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+            reinterpret_cast<uint4*>(dlo)[1] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+            if(hi_ok)
+            {
+                reinterpret_cast<uint4*>(dhi)[0] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                reinterpret_cast<uint4*>(dhi)[1] = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+            }
         }
         else
         {
-            for(int i = 0; i < min(32, K - k0); ++i) dst[i] = uint16_t(o[i / 2] >> (16 * (i & 1)));
+            for(int i = 0; i < min(16, K - k0); ++i)
+            {
+                dlo[i] = uint16_t(lo[i / 2] >> (16 * (i & 1)));
+                if(hi_ok) dhi[i] = uint16_t(hi[i / 2] >> (16 * (i & 1)));
+            }
         }
     }
 }
@@ -115,8 +134,8 @@ int run_wq_prefill(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, void* w
     const int blocks = 148 * 8;
     if(p.b_op == CKB_BOP_GROUP)
     {
-        const int n_tiles = (p.N + 127) / 128, k_tiles = (p.K + 127) / 128;
-        const long long chunks = (long long)n_tiles * k_tiles * 512;
+        const int n_groups = (p.N + 15) / 16, k_tiles = (p.K + 63) / 64;
+        const long long chunks = (long long)n_groups * k_tiles * 32;
         if(f16)
             wq_dequant_w4_kernel<true><<<blocks, 256, 0, stream>>>(static_cast<const uint8_t*>(p.b), static_cast<const uint16_t*>(p.scale),
                                                                    static_cast<const uint8_t*>(p.zero), p.zero_const, p.N, p.K, k_tiles, chunks, bdq);

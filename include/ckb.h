@@ -150,7 +150,7 @@ typedef struct ckb_gemm_plan {
     uint64_t algo_bytes;     /* algorithmic HBM bytes of one launch: A + B + scales[/zp] + D + E */
     uint64_t flops;          /* 2*M*N*K */
     /* TMA descriptors etc. encoded at query time for exactly the pointers in the problem */
-    unsigned char opaque[640] __attribute__((aligned(64)));
+    unsigned char opaque[1280] __attribute__((aligned(64)));
 } ckb_gemm_plan;
 
 /* Validate the problem, choose the kernel, size the workspace, encode the TMA descriptors.

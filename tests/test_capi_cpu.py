@@ -112,7 +112,7 @@ def test_algorithmic_byte_and_flop_accounting():
         rc, plan, _ = _query(p)
         assert plan.algo_bytes == want and plan.flops == 2 * M * 4096 * 4096
     assert capi.lib().ckb_prepack_b_int4_bytes(4096, 4096) == 4096 * 4096 // 2
-    assert capi.lib().ckb_prepack_b_int4_bytes(1000, 130) == 8 * 2 * 8192  # padded to whole 128x128 tiles
+    assert capi.lib().ckb_prepack_b_int4_bytes(1000, 130) == 63 * 3 * 512  # padded to whole 16-channel x 64-k fragments blocks
 
 
 def test_product_never_imports_the_oracle():

@@ -242,7 +242,8 @@ def test_host_buffer_entry_point_matches_device_path():
     he = torch.zeros(M, N, dtype=torch.int16).pin_memory()
     p.a, p.e = ha.data_ptr(), he.data_ptr()
     staging = torch.empty(int(capi.lib().ckb_gemm_host_staging_bytes(C.byref(p))), dtype=torch.uint8, device="cuda")
-    capi.check(capi.lib().ckb_gemm_run_host(C.byref(p), staging.data_ptr(), op.workspace.data_ptr(),
+    ws = op.workspace.data_ptr() if op.workspace is not None else None
+    capi.check(capi.lib().ckb_gemm_run_host(C.byref(p), staging.data_ptr(), ws,
                                             torch.cuda.current_stream().cuda_stream))
     assert np.array_equal(he.numpy().view(np.uint16), ref)
 
