@@ -108,6 +108,21 @@ __device__ __forceinline__ void dequant_w4_word_scaled2(uint32_t w, uint32_t zm_
     }
 }
 
+// Same word, exact part only: (q - zp) in A's type (no rounding at all); the caller applies the group scale to the
+// fp32 partial sums (CK's ab_scale host pattern scales in float: gemm_multiply_multiply_xdl_fp8_ab_scale.cpp:258-290).
+template <bool F16>
+__device__ __forceinline__ void dequant_w4_word_exact2(uint32_t w, uint32_t zm_lo, uint32_t zm_hi, uint32_t* out4)
+{
+    constexpr uint32_t MAGIC = F16 ? 0x64006400u : 0x43004300u;
+#pragma unroll
+    for(int i = 0; i < 4; ++i)
+    {
+        const uint32_t t  = lop3<0xEA>(w >> (4 * i), 0x000F000Fu, MAGIC);
+        const uint32_t zm = (i & 1) ? zm_hi : zm_lo;
+        out4[i] = F16 ? hsub2_f16(t, zm) : hsub2_bf16(t, zm);
+    }
+}
+
 // ---- W8 fpAintB (fp16): u8 -> 0x6400|u8 = 1024 + u8; minus 1152 (= 0x6480) removes the +128 bias
 // (the reference's own trick, unary_element_wise_operation.hpp:1061-1091); times scale: ONE rounding.
 __device__ __forceinline__ void dequant_u8x4_fpaintb(uint32_t w, uint32_t scale2, uint32_t* out2)

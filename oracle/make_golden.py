@@ -38,9 +38,12 @@ def case_w4a16(name, M, N, K, seed, with_zero, f16=False):
         dt = orc.BF16
     z = rng.integers(0, 16, (K // G, N)).astype(np.uint8) if with_zero else np.zeros((0, 0), np.uint8)
     kw = dict(scale=s, s_dtype=dt, zero=z if with_zero else None, zero_const=8, group_size=G)
-    e_rtn = orc.gemm(a, dt, q, orc.U8, dt, b_op=orc.BOP_GROUP_RTN, **kw)
+    # e / e_f32: the decode definition (exact (q - zp), group scale applied in fp32 -- CK's ab_scale host pattern);
+    # e_rtn: (q - zp) * s rounded once into A's type first, what the prefill path feeds the dense tensor-core GEMM
+    e     = orc.gemm(a, dt, q, orc.U8, dt, b_op=orc.BOP_GROUP_F32, **kw)
     e_f32 = orc.gemm(a, dt, q, orc.U8, orc.F32, b_op=orc.BOP_GROUP_F32, **kw)
-    np.savez_compressed(os.path.join(OUT, name), kind="w4a16", a=a, q=q, s=s, z=z, f16=f16, e=e_rtn, e_f32=e_f32)
+    e_rtn = orc.gemm(a, dt, q, orc.U8, dt, b_op=orc.BOP_GROUP_RTN, **kw)
+    np.savez_compressed(os.path.join(OUT, name), kind="w4a16", a=a, q=q, s=s, z=z, f16=f16, e=e, e_f32=e_f32, e_rtn=e_rtn)
 
 
 def case_w8a16_bf16(name, M, N, K, seed, cde):

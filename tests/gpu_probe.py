@@ -112,7 +112,7 @@ def _w4_case(M, N, K, name, with_zero=False, f16=False, onehot=False):
         for m in range(M):
             a_np[m, (m * 37) % K] = np.float16(1.0) if f16 else 0x3F80
     z = rng.integers(0, 16, (K // G, N)).astype(np.uint8) if with_zero else None
-    ref = orc.gemm(a_np, adt, q, orc.U8, orc.F32, b_op=orc.BOP_GROUP_RTN, scale=s_np, s_dtype=adt, zero=z,
+    ref = orc.gemm(a_np, adt, q, orc.U8, orc.F32, b_op=orc.BOP_GROUP_F32, scale=s_np, s_dtype=adt, zero=z,
                    zero_const=8, group_size=G)
     to_t = lambda x: (torch.from_numpy(x).cuda() if f16 else torch.from_numpy(x.view(np.int16)).cuda().view(torch.bfloat16))
     ad, sd = to_t(a_np), to_t(s_np)

@@ -11,6 +11,26 @@ from composable_kernel_b200 import capi, ops  # noqa: E402
 
 
 def timeit(ops_list, iters=20):
+    if os.environ.get("PERF_GRAPH"):
+        # CUDA-graph replay of the whole rotation (launch overhead of the host API taken out)
+        st = torch.cuda.Stream()
+        with torch.cuda.stream(st):
+            for op in ops_list:
+                op.run(st.cuda_stream)
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=st):
+                for op in ops_list:
+                    op.run(st.cuda_stream)
+            g.replay()
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(st)
+            for _ in range(iters):
+                g.replay()
+            b.record(st)
+            torch.cuda.synchronize()
+        return a.elapsed_time(b) * 1e3 / (iters * len(ops_list))
     s = torch.cuda.current_stream().cuda_stream
     for op in ops_list:
         op.run(s)
