@@ -8,13 +8,13 @@ namespace ckb {
 namespace {
 
 struct GVLayout { int off_w, off_s, off_z, stage_bytes, scratch; };
-GVLayout gv_layout(int M, int nt, int g, bool zp)
+GVLayout gv_layout(int M, int nt, int g, bool zp, int kbw)
 {
     GVLayout l;
-    l.off_w       = (GV_CHUNK_KB * M * 128 + 1023) & ~1023;
-    l.off_s       = l.off_w + g * GV_CHUNK_KB * 512;
-    l.off_z       = l.off_s + GV_PAIRS * g * 32;
-    l.stage_bytes = (l.off_z + (zp ? GV_PAIRS * g * 16 : 0) + 1023) & ~1023;
+    l.off_w       = (kbw * GV_CHUNK_KB * M * 128 + 1023) & ~1023;
+    l.off_s       = l.off_w + g * kbw * GV_CHUNK_KB * 512;
+    l.off_z       = l.off_s + kbw * GV_PAIRS * g * 32;
+    l.stage_bytes = (l.off_z + (zp ? kbw * GV_PAIRS * g * 16 : 0) + 1023) & ~1023;
     l.scratch     = GV_PAIRS * g * nt * 512;
     return l;
 }
@@ -43,7 +43,7 @@ int plan_wq_gemv(const ckb_gemm_problem& p, ckb_gemm_plan& plan)
     const bool zp  = p.zero != nullptr;
     const int nt   = p.M <= 8 ? 1 : (p.M <= 16 ? 2 : (p.M <= 32 ? 4 : 8));
     const int n_groups = (p.N + 15) / 16, kb_total = (p.K + 63) / 64, kg_total = (p.K + 127) / 128;
-    const int n_chunks = (kb_total + GV_CHUNK_KB - 1) / GV_CHUNK_KB;
+    int n_chunks       = (kb_total + GV_CHUNK_KB - 1) / GV_CHUNK_KB;
     const int sms      = device_info().sm_count > 0 ? device_info().sm_count : 148;
     int grid           = std::min(sms, n_groups);
     if(const char* e = getenv("CKB_GEMV_GRID")) grid = std::max(1, std::min(atoi(e), n_groups));
@@ -53,7 +53,7 @@ int plan_wq_gemv(const ckb_gemm_problem& p, ckb_gemm_plan& plan)
     int gmax = gv_gmax(nt);
     while(gmax > 1)
     {
-        const GVLayout l = gv_layout(p.M, nt, gmax, zp);
+        const GVLayout l = gv_layout(p.M, nt, gmax, zp, 1);
         if(std::min(2, n_chunks) * l.stage_bytes + l.scratch <= budget) break;
         --gmax;
     }
@@ -62,15 +62,18 @@ int plan_wq_gemv(const ckb_gemm_problem& p, ckb_gemm_plan& plan)
     const int n_slots = grid * passes;
     const int g_hi    = (n_groups + n_slots - 1) / n_slots;
     const int g_lo    = std::max(1, n_groups / n_slots);
-    const GVLayout l  = gv_layout(p.M, nt, g_hi, zp);
+    const int kbw     = gv_kbw(nt, g_hi);   // 64-k blocks per warp and stage (compile-time property of the variant)
+    const int chunk_kb = GV_CHUNK_KB * kbw;
+    n_chunks          = (kb_total + chunk_kb - 1) / chunk_kb;
+    const GVLayout l  = gv_layout(p.M, nt, g_hi, zp, kbw);
     gp->off_w = l.off_w; gp->off_s = l.off_s; gp->off_z = l.off_z; gp->stage_bytes = l.stage_bytes;
     {
         // small variants (NT = 1, GW <= 3) are compiled for two resident CTAs per SM so that, under programmatic dependent
         // launch, the NEXT kernel's prologue and weight prefill overlap this one: keep the footprint under half an SM
-        // when that still leaves a useful ring (>= 3 stages or the whole problem)
+        // when the whole problem still fits in the ring (no refills); otherwise a deep ring matters more
         const int gw   = g_hi;
         const int half = 112 * 1024 - 1280;
-        if(nt == 1 && gw <= 3 && !getenv("CKB_GEMV_SMEM_KB") && (half - l.scratch) / l.stage_bytes >= std::min(passes * n_chunks, 3))
+        if(nt == 1 && gw <= 3 && !getenv("CKB_GEMV_SMEM_KB") && (half - l.scratch) / l.stage_bytes >= passes * n_chunks)
             budget = half;
     }
     gp->stages = std::min({GV_MAX_STAGES, (budget - l.scratch) / l.stage_bytes, passes * n_chunks});
@@ -84,7 +87,7 @@ int plan_wq_gemv(const ckb_gemm_problem& p, ckb_gemm_plan& plan)
     {   // activations as [K/64][M][64]: box = 16 k-blocks x M rows x 64 k, 128B swizzle
         const uint64_t dims[3] = {64, uint64_t(p.M), uint64_t(kb_total)};
         const uint64_t str[2]  = {uint64_t(p.lda) * 2, 128};
-        const uint32_t box[3]  = {64, uint32_t(p.M), GV_CHUNK_KB};
+        const uint32_t box[3]  = {64, uint32_t(p.M), uint32_t(chunk_kb)};
         if(int rc = encode_tmap_nd(&gp->tmA, adt, 3, p.a, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B)) return rc;
     }
     for(int i = 0; i < 2; ++i)
@@ -93,20 +96,20 @@ int plan_wq_gemv(const ckb_gemm_problem& p, ckb_gemm_plan& plan)
         {   // packed weights [n16 group][k64 block][128 words]
             const uint64_t dims[3] = {128, uint64_t(kb_total), uint64_t(n_groups)};
             const uint64_t str[2]  = {512, uint64_t(kb_total) * 512};
-            const uint32_t box[3]  = {128, GV_CHUNK_KB, uint32_t(gb)};
+            const uint32_t box[3]  = {128, uint32_t(chunk_kb), uint32_t(gb)};
             if(int rc = encode_tmap_nd(&gp->tmW[i], CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, p.b, dims, str, box, CU_TENSOR_MAP_SWIZZLE_NONE)) return rc;
         }
         {   // group scales [K/128][N]
             const uint64_t dims[2] = {uint64_t(p.N), uint64_t(kg_total)};
             const uint64_t str[1]  = {uint64_t(p.N) * 2};
-            const uint32_t box[2]  = {uint32_t(16 * gb), GV_PAIRS};
+            const uint32_t box[2]  = {uint32_t(16 * gb), uint32_t(GV_PAIRS * kbw)};
             if(int rc = encode_tmap_nd(&gp->tmS[i], adt, 2, p.scale, dims, str, box, CU_TENSOR_MAP_SWIZZLE_NONE)) return rc;
         }
         if(zp)
         {
             const uint64_t dims[2] = {uint64_t(p.N), uint64_t(kg_total)};
             const uint64_t str[1]  = {uint64_t(p.N)};
-            const uint32_t box[2]  = {uint32_t(16 * gb), GV_PAIRS};
+            const uint32_t box[2]  = {uint32_t(16 * gb), uint32_t(GV_PAIRS * kbw)};
             if(int rc = encode_tmap_nd(&gp->tmZ[i], CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, p.zero, dims, str, box, CU_TENSOR_MAP_SWIZZLE_NONE)) return rc;
         }
         else

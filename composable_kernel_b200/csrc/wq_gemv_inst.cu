@@ -15,7 +15,9 @@ namespace ckb {
 int GV_FN(int nt, int gw, const GVPlan* gp, const GVArgs& a, int grid, cudaStream_t st)
 {
     constexpr bool F16 = GV_INST_F16 != 0;
-#define GV_CASE(NT_, GW_) if(nt == NT_ && gw == GW_) return launch_gemv<NT_, GW_, F16>(gp, a, grid, st);
+#define GV_CASE(NT_, GW_)                                                                                      \
+    if(nt == NT_ && gw == GW_)                                                                                 \
+        return a.has_zero ? launch_gemv<NT_, GW_, F16, true>(gp, a, grid, st) : launch_gemv<NT_, GW_, F16, false>(gp, a, grid, st);
 #if GV_INST_NT == 1
     GV_CASE(1, 1) GV_CASE(1, 2) GV_CASE(1, 3) GV_CASE(1, 4) GV_CASE(1, 5) GV_CASE(1, 6) GV_CASE(1, 7) GV_CASE(1, 8)
     GV_CASE(1, 9) GV_CASE(1, 10) GV_CASE(1, 11) GV_CASE(1, 12) GV_CASE(1, 13) GV_CASE(1, 14) GV_CASE(1, 15) GV_CASE(1, 16)

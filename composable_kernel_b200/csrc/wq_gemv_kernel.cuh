@@ -35,7 +35,10 @@ namespace ckb {
 constexpr int GV_PAIRS     = 8;                       // warp pairs; pair p owns the 128-k group p of every stage
 constexpr int GV_CONSUMERS = 2 * GV_PAIRS;            // consumer warps
 constexpr int GV_THREADS   = 32 * GV_CONSUMERS;       // lane 0 of warp 0 doubles as the TMA producer
-constexpr int GV_CHUNK_KB  = 2 * GV_PAIRS;            // 64-k blocks per stage (1024 k)
+constexpr int GV_CHUNK_KB  = 2 * GV_PAIRS;            // 64-k blocks per stage (1024 k) for one block per warp
+// slots of <= 2 groups give a warp only 8 weight words per 64-k block: those variants take TWO blocks per warp and stage
+// (2048 k per stage), halving the per-stage overhead (barrier wait, fragment loads, scale loads, release)
+__host__ __device__ constexpr int gv_kbw(int nt, int gw) { return (gw <= 2 && nt <= 2) ? 2 : 1; }
 constexpr int GV_MAX_STAGES = 12;
 
 struct GVArgs
@@ -99,7 +102,7 @@ static __device__ __noinline__ void gv_store_one(const EpiParams& ep, int m, int
 
 // small variants are built for two resident CTAs per SM, so that under programmatic dependent launch the NEXT kernel's
 // CTAs (prologue, tensor-map fetch, weight prefill) overlap the tail of the current one
-template <int NT, int GW, bool F16>
+template <int NT, int GW, bool F16, bool ZP>
 __global__ void __launch_bounds__(GV_THREADS, (NT == 1 && GW <= 3) ? 2 : 1)
 wq_gemv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW0,
                const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ CUtensorMap tmS0,
@@ -108,6 +111,9 @@ wq_gemv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 {
     // GW = groups of 16 channels per slot (= g_hi of the launch; slots with g_hi - 1 groups run one dead group)
     constexpr uint32_t MAGIC16 = F16 ? 0x6400u : 0x4300u;
+    constexpr int KBW      = gv_kbw(NT, GW);       // 64-k blocks per warp and stage
+    constexpr int CHUNK_KB = GV_CHUNK_KB * KBW;    // 64-k blocks per stage
+    constexpr int SROWS    = GV_PAIRS * KBW;       // 128-k scale groups per stage
 
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -138,7 +144,7 @@ wq_gemv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if(threadIdx.x == 0) GV_GT(1);
     if(GV_DBG(4)) return; // debug: launch-rate floor (prologue only)
 
-    const int n_chunks = (args.kb_total + GV_CHUNK_KB - 1) / GV_CHUNK_KB;
+    const int n_chunks = (args.kb_total + CHUNK_KB - 1) / CHUNK_KB;
     const int slot0    = blockIdx.x * args.passes;
     const int RB       = args.act_rows; // activation rows per 64-k block in a stage (= M)
     auto slot_range = [&](int slot, int& gbeg, int& G) {
@@ -151,7 +157,7 @@ wq_gemv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // (slot, chunk) cursor: the slot's group range is computed once per slot (64-bit divisions are ~150 clk each)
     struct Cur { int ps, c, gbeg, G; };
     const int total          = args.passes * n_chunks;
-    const uint32_t act_bytes = GV_CHUNK_KB * RB * 128;
+    const uint32_t act_bytes = CHUNK_KB * RB * 128;
     const bool is_producer   = (threadIdx.x == 0);
     uint64_t pol_stream      = 0;
     auto cur_next = [&](Cur& q) {
@@ -164,27 +170,27 @@ wq_gemv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     auto issue_weights = [&](int s, const Cur& q) {
         const uint32_t st = smem_base + s * args.stage_bytes;
         const bool hi     = (q.G == args.g_hi);
-        uint32_t bytes    = act_bytes + q.G * (GV_CHUNK_KB * 512 + GV_PAIRS * 32);
-        if(args.has_zero) bytes += GV_PAIRS * q.G * 16;
+        uint32_t bytes    = act_bytes + q.G * (CHUNK_KB * 512 + SROWS * 32);
+        if(ZP) bytes += SROWS * q.G * 16;
         if(GV_DBG(2))
         {
-            const int nkb = min(GV_CHUNK_KB, args.kb_total - q.c * GV_CHUNK_KB);
-            bytes -= q.G * (GV_CHUNK_KB - nkb) * 512;
+            const int nkb = min(CHUNK_KB, args.kb_total - q.c * CHUNK_KB);
+            bytes -= q.G * (CHUNK_KB - nkb) * 512;
             ptx::mbar_arrive_expect_tx(full_bar(s), bytes);
             for(int gi = 0; gi < q.G; ++gi)
-                ptx::bulk_load_1d(st + args.off_w + gi * (GV_CHUNK_KB * 512),
-                                  args.w + ((size_t)(q.gbeg + gi) * args.kb_total + q.c * GV_CHUNK_KB) * 512, nkb * 512, full_bar(s), pol_stream);
+                ptx::bulk_load_1d(st + args.off_w + gi * (CHUNK_KB * 512),
+                                  args.w + ((size_t)(q.gbeg + gi) * args.kb_total + q.c * CHUNK_KB) * 512, nkb * 512, full_bar(s), pol_stream);
         }
         else
         {
         ptx::mbar_arrive_expect_tx(full_bar(s), bytes);
-        ptx::tma_load_3d_hint(st + args.off_w, hi ? &tmW0 : &tmW1, full_bar(s), 0, q.c * GV_CHUNK_KB, q.gbeg, pol_stream);
+        ptx::tma_load_3d_hint(st + args.off_w, hi ? &tmW0 : &tmW1, full_bar(s), 0, q.c * CHUNK_KB, q.gbeg, pol_stream);
         }
-        ptx::tma_load_2d(st + args.off_s, hi ? &tmS0 : &tmS1, full_bar(s), q.gbeg * 16, q.c * GV_PAIRS);
-        if(args.has_zero) ptx::tma_load_2d(st + args.off_z, hi ? &tmZ0 : &tmZ1, full_bar(s), q.gbeg * 16, q.c * GV_PAIRS);
+        ptx::tma_load_2d(st + args.off_s, hi ? &tmS0 : &tmS1, full_bar(s), q.gbeg * 16, q.c * SROWS);
+        if(ZP) ptx::tma_load_2d(st + args.off_z, hi ? &tmZ0 : &tmZ1, full_bar(s), q.gbeg * 16, q.c * SROWS);
     };
     auto issue_acts = [&](int s, int c) {
-        ptx::tma_load_3d(smem_base + s * args.stage_bytes, &tmA, full_bar(s), 0, 0, c * GV_CHUNK_KB);
+        ptx::tma_load_3d(smem_base + s * args.stage_bytes, &tmA, full_bar(s), 0, 0, c * CHUNK_KB);
     };
     Cur qw{0, 0, 0, 0};
     int p_issued = 0, p_s = 0;
@@ -225,7 +231,7 @@ wq_gemv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             p_issued = pre;
         }
     }
-    const int p_defer = args.stages >= 3 ? 1 : 0; // refill a slot one iteration after warp 0 released it: no stall on stragglers
+    const int p_defer = args.stages >= 4 ? 1 : 0; // refill a slot one iteration after warp 0 released it: no stall on stragglers
     {
         // ===================== consumers: ld.shared -> dequant -> HMMA =====================
         // Warp w owns the 64-k block w of every stage and runs all G groups of the slot against it: the activation
@@ -234,18 +240,23 @@ wq_gemv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int g = lane >> 2, t = lane & 3;
         const int tid  = threadIdx.x;
         const EpiParams& ep = args.ep;
-        uint32_t a_addr[NT][2]; // activation fragment chunks (128B-swizzled rows [kb][m][64 k]) relative to the stage
+        uint32_t a_addr[KBW][NT][2]; // activation fragment chunks (128B-swizzled rows [kb][m][64 k]) relative to the stage
         bool a_ok[NT];
 #pragma unroll
         for(int nt = 0; nt < NT; ++nt)
         {
-            const int r        = 8 * nt + g;
-            const uint32_t rix = warp * RB + r; // row of the stage's activation box
-            a_ok[nt]           = r < RB;
-            a_addr[nt][0]      = rix * 128 + (((2 * t) ^ (rix & 7)) << 4);
-            a_addr[nt][1]      = rix * 128 + (((2 * t + 1) ^ (rix & 7)) << 4);
+            const int r = 8 * nt + g;
+            a_ok[nt]    = r < RB;
+#pragma unroll
+            for(int b = 0; b < KBW; ++b)
+            {
+                const uint32_t rix = (warp * KBW + b) * RB + r; // row of the stage's activation box
+                a_addr[b][nt][0]   = rix * 128 + (((2 * t) ^ (rix & 7)) << 4);
+                a_addr[b][nt][1]   = rix * 128 + (((2 * t + 1) ^ (rix & 7)) << 4);
+            }
         }
-        const uint32_t w_off = args.off_w + warp * 512 + lane * 16;
+        const uint32_t w_off = args.off_w + warp * KBW * 512 + lane * 16;
+        const int srow       = (warp * KBW) >> 1; // this warp's 128-k scale group inside the stage
         uint32_t st   = smem_base;   // current stage
         uint32_t fbar = full_bar(0);
         int it = 0, s = 0;
@@ -254,8 +265,8 @@ wq_gemv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         {
             int gbeg, G;
             slot_range(slot0 + ps, gbeg, G);
-            const uint32_t s_off = args.off_s + ((warp >> 1) * 16 * G + g) * 2; // this warp's 128-k group row: [8][16 G]
-            const uint32_t z_off = args.off_z + (warp >> 1) * 16 * G + g;
+            const uint32_t s_off = args.off_s + (srow * 16 * G + g) * 2; // this warp's 128-k group row: [SROWS][16 G]
+            const uint32_t z_off = args.off_z + srow * 16 * G + g;
             float acc[GW][NT][4];
 #pragma unroll
             for(int gi = 0; gi < GW; ++gi)
@@ -270,55 +281,62 @@ wq_gemv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 if(tid == 0 && it == 0) GV_GT(3);
                 if(tid == 0 && it == 0) GV_SPAN_MIN(2);
                 GV_CT(it, 0);
-                if(c * GV_CHUNK_KB + warp < args.kb_total && !GV_DBG(1))
+                if(c * CHUNK_KB + warp * KBW < args.kb_total && !GV_DBG(1))
                 {
-                    uint4 bf[NT][2];
+                    // (a block past the end of K holds zero-filled activations and weights: computing it is harmless)
+                    uint4 bf[KBW][NT][2];
 #pragma unroll
-                    for(int nt = 0; nt < NT; ++nt)
-                    {
-                        if(a_ok[nt])
+                    for(int b = 0; b < KBW; ++b)
+#pragma unroll
+                        for(int nt = 0; nt < NT; ++nt)
                         {
-                            bf[nt][0] = ptx::lds128(st + a_addr[nt][0]);
-                            bf[nt][1] = ptx::lds128(st + a_addr[nt][1]);
+                            if(a_ok[nt])
+                            {
+                                bf[b][nt][0] = ptx::lds128(st + a_addr[b][nt][0]);
+                                bf[b][nt][1] = ptx::lds128(st + a_addr[b][nt][1]);
+                            }
+                            else
+                                bf[b][nt][0] = bf[b][nt][1] = make_uint4(0u, 0u, 0u, 0u);
                         }
-                        else
-                            bf[nt][0] = bf[nt][1] = make_uint4(0u, 0u, 0u, 0u);
-                    }
                     // All GW groups unconditionally (no branches between groups: the scheduler overlaps one group's
                     // HMMAs with the next group's unpack).  A slot with GW - 1 groups computes one dead group on whatever
                     // the stage holds there; its accumulators are never stored.
 #pragma unroll
                     for(int gi = 0; gi < GW; ++gi)
                     {
-                        const uint4 wv    = ptx::lds128(st + w_off + gi * (GV_CHUNK_KB * 512));
                         const uint32_t sl = ptx::lds_u16(st + s_off + gi * 32), sh = ptx::lds_u16(st + s_off + gi * 32 + 16);
                         uint32_t zm_lo, zm_hi;
-                        if(args.has_zero)
+                        if(ZP)
                         {
                             zm_lo = (MAGIC16 + ptx::lds_u8(st + z_off + gi * 16)) * 0x10001u;
                             zm_hi = (MAGIC16 + ptx::lds_u8(st + z_off + gi * 16 + 8)) * 0x10001u;
                         }
                         else
                             zm_lo = zm_hi = (MAGIC16 + uint32_t(args.zero_const)) * 0x10001u;
-                        // exact (q - zp) in A's type -> fp32 partial sums of this 64-k block
+                        // exact (q - zp) in A's type -> fp32 partial sums of this warp's 64 / 128 k (one scale group)
                         float part[NT][4];
 #pragma unroll
                         for(int nt = 0; nt < NT; ++nt) part[nt][0] = part[nt][1] = part[nt][2] = part[nt][3] = 0.f;
-                        const uint32_t w4[4] = {wv.x, wv.y, wv.z, wv.w};
 #pragma unroll
-                        for(int ks = 0; ks < 4; ++ks)
+                        for(int b = 0; b < KBW; ++b)
                         {
-                            uint32_t a[4];
-                            dequant_w4_word_exact2<F16>(w4[ks], zm_lo, zm_hi, a);
+                            const uint4 wv       = ptx::lds128(st + w_off + b * 512 + gi * (CHUNK_KB * 512));
+                            const uint32_t w4[4] = {wv.x, wv.y, wv.z, wv.w};
 #pragma unroll
-                            for(int nt = 0; nt < NT; ++nt)
+                            for(int ks = 0; ks < 4; ++ks)
                             {
-                                const uint4 b = bf[nt][ks >> 1];
-                                if(ks & 1) ptx::mma_m16n8k16<F16>(part[nt], a, b.z, b.w);
-                                else ptx::mma_m16n8k16<F16>(part[nt], a, b.x, b.y);
+                                uint32_t a[4];
+                                dequant_w4_word_exact2<F16>(w4[ks], zm_lo, zm_hi, a);
+#pragma unroll
+                                for(int nt = 0; nt < NT; ++nt)
+                                {
+                                    const uint4 bb = bf[b][nt][ks >> 1];
+                                    if(ks & 1) ptx::mma_m16n8k16<F16>(part[nt], a, bb.z, bb.w);
+                                    else ptx::mma_m16n8k16<F16>(part[nt], a, bb.x, bb.y);
+                                }
                             }
                         }
-                        // the block lies inside one scale group: apply the (group, channel) scale to the partial sums
+                        // apply the (group, channel) scale to the partial sums
                         const float s_lo = F16 ? __half2float(__ushort_as_half((unsigned short)sl)) : __uint_as_float(sl << 16);
                         const float s_hi = F16 ? __half2float(__ushort_as_half((unsigned short)sh)) : __uint_as_float(sh << 16);
 #pragma unroll
@@ -423,10 +441,10 @@ struct GVPlan
 // per-(dtype, NT) launchers: each lives in its own translation unit (wq_gemv_inst.cu compiled with -DGV_INST_F16 / -DGV_INST_NT)
 int launch_gemv_variant(bool f16, int nt, int gw, const GVPlan* gp, const GVArgs& a, int grid, cudaStream_t stream);
 
-template <int NT, int GW, bool F16>
+template <int NT, int GW, bool F16, bool ZP>
 static int launch_gemv(const GVPlan* gp, const GVArgs& a, int grid, cudaStream_t stream)
 {
-    auto kfn = wq_gemv_kernel<NT, GW, F16>;
+    auto kfn = wq_gemv_kernel<NT, GW, F16, ZP>;
     static bool attr_set = false;
     if(!attr_set)
     {
