@@ -354,24 +354,31 @@ def main():
         dist.destroy_process_group()
 
 
-def cpu_baseline():
-    """The oracle (kind 'port') on the host cores, bounded sample: one layer's GEMMs at M=4."""
+def cpu_baseline(min_seconds=10.0):
+    """The oracle (kind 'port': restated ReferenceGemm, all host threads) on a bounded sample of the same workload:
+    the three layer shapes at M in {1,4,16}, repeated until >= min_seconds of CPU work."""
     import numpy as np
     from oracle import ck_oracle as orc
     rng = np.random.default_rng(0)
-    M = 4
-    t_total, nbytes = 0.0, 0
+    t_total, nbytes, n_gemm = 0.0, 0, 0
+    probs = []
     for (N, K) in sorted(set(LAYER_SHAPES)):
-        a = orc.bf16_trunc(rng.standard_normal((M, K)).astype(np.float32))
         q = rng.integers(0, 16, (K, N), dtype=np.uint8)
         s = orc.bf16_trunc((rng.random((K // GROUP, N)) * 0.015 + 0.005).astype(np.float32))
-        t0 = time.perf_counter()
-        orc.gemm(a, orc.BF16, q, orc.U8, orc.BF16, b_op=orc.BOP_GROUP_F32, scale=s, s_dtype=orc.BF16,
-                 zero_const=8, group_size=GROUP)
-        t_total += time.perf_counter() - t0
-        nbytes += algo_bytes(M, N, K)
+        probs.append((N, K, q, s))
+    while t_total < min_seconds:
+        for M in MS:
+            for (N, K, q, s) in probs:
+                a = orc.bf16_trunc(rng.standard_normal((M, K)).astype(np.float32))
+                t0 = time.perf_counter()
+                orc.gemm(a, orc.BF16, q, orc.U8, orc.BF16, b_op=orc.BOP_GROUP_F32, scale=s, s_dtype=orc.BF16,
+                         zero_const=8, group_size=GROUP)
+                t_total += time.perf_counter() - t0
+                nbytes += algo_bytes(M, N, K)
+                n_gemm += 1
     return {"value": nbytes / t_total / 1e9, "unit": "GB/s", "cores": orc.lib().orc_hardware_threads(),
-            "kind": "port", "sample": "one GEMM of each of the 3 shapes at M=4 (restated ReferenceGemm, ab_scale pattern)",
+            "kind": "port", "sample": f"{n_gemm} GEMMs: the 3 layer shapes x M in {{1,4,16}}, repeated for >= {min_seconds:.0f} s "
+                                      "(restated ReferenceGemm, ab_scale host pattern, all host threads)",
             "seconds": t_total}
 
 
