@@ -83,13 +83,17 @@ def lib():
         l.ckb_prepack_b_int4_bytes.restype = C.c_uint64
         l.ckb_prepack_b_int4.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_void_p,
                                          C.c_void_p]
+        l.ckb_grouped_gemm_arg_bytes.argtypes = [C.c_int32, C.c_int32]
+        l.ckb_grouped_gemm_arg_bytes.restype = C.c_uint64
+        l.ckb_grouped_gemm_query.argtypes = [C.POINTER(GemmProblem), C.c_int32]
+        l.ckb_grouped_gemm_run.argtypes = [C.POINTER(GemmProblem), C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]
         _lib = l
     return _lib
 
 
 EXPORTED = [
     "ckb_gemm_query", "ckb_gemm_run", "ckb_gemm_host_staging_bytes", "ckb_gemm_run_host",
-    "ckb_prepack_b_u8", "ckb_prepack_b_rowmajor_i8", "ckb_prepack_b_int4_bytes", "ckb_prepack_b_int4", "ckb_grouped_gemm_run",
+    "ckb_prepack_b_u8", "ckb_prepack_b_rowmajor_i8", "ckb_prepack_b_int4_bytes", "ckb_prepack_b_int4", "ckb_grouped_gemm_run", "ckb_grouped_gemm_query", "ckb_grouped_gemm_arg_bytes",
     "ckb_last_error", "ckb_version", "ckb_device_sm_count",
 ]
 

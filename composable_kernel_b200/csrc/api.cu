@@ -284,9 +284,25 @@ int ckb_prepack_b_int4(const void* src, int64_t sk, int64_t sn, int32_t N, int32
     return launch_prepack_int4(src, sk, sn, N, K, dst, static_cast<cudaStream_t>(stream));
 }
 
-int ckb_grouped_gemm_run(const ckb_gemm_problem*, const ckb_group_arg*, int32_t, int32_t, void*)
+uint64_t ckb_grouped_gemm_arg_bytes(int32_t num_b, int32_t num_d)
 {
-    return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM not built yet");
+    if(num_b < 1 || num_b > 2 || num_d < 0 || num_d > 1) return 0;
+    return uint64_t(grouped_arg_bytes(num_b, num_d));
+}
+
+int ckb_grouped_gemm_query(const ckb_gemm_problem* proto, int32_t group_count)
+{
+    if(!proto) return set_error(CKB_ERR_INVALID, "null problem");
+    return check_grouped(*proto, group_count);
+}
+
+int ckb_grouped_gemm_run(const ckb_gemm_problem* proto, const void* dev_args, int32_t group_count, int32_t sum_m, void* stream)
+{
+    if(!proto) return set_error(CKB_ERR_INVALID, "null problem");
+    if(group_count < 0 || sum_m < 0) return set_error(CKB_ERR_INVALID, "negative group count / row count");
+    if(int rc = check_grouped(*proto, group_count)) return rc;
+    if(!device_info().ok) return set_error(CKB_ERR_NO_DEVICE, "no sm_100 device");
+    return run_grouped(*proto, dev_args, group_count, sum_m, static_cast<cudaStream_t>(stream));
 }
 
 } // extern "C"

@@ -1,0 +1,288 @@
+// grouped_gemm.cu -- K4: grouped GEMM with fixed N,K and a DEVICE-resident argument array.
+// Replaces kernel_grouped_gemm_xdl_fixed_nk (device/impl/device_grouped_gemm_multi_abd_xdl_fixed_nk.hpp:37-145):
+// G independent GEMMs  E_g[M_g,N] = cde( A_g[M_g,K] * bop(B0_g[K,N], B1_g[N]), D0_g ), M_g read on the device.
+// The reference gives every group the same number of workgroups (sized for the average M, :510-517) and lets each
+// loop over its group's tiles; here ONE persistent grid walks the concatenated tile list of all groups, so a group
+// with few rows does not hold idle CTAs.  Pointers live in device memory, so no host-encoded TMA descriptor can
+// describe them: tiles are fetched with 16-byte global loads (register prefetch of the next k-tile under the
+// current tile's MMAs), the int8 weight is expanded with the Multiply B-functor
+// (binary_element_wise_operation.hpp:184-190: bf16( float(int8) * float(bf16 scale) ), truncating) on its way
+// into shared memory, fragments come from ldmatrix, products accumulate in fp32 registers (HMMA m16n8k16).
+// The client-31 problem (16 groups x ~48 rows x 1024 x 512) is ~10 MB / 0.8 GFLOP: launch- and HBM-bound.
+#include "common.cuh"
+#include "epilogue.cuh"
+#include "kernels.h"
+#include "ptx.cuh"
+
+namespace ckb {
+namespace {
+
+constexpr int GG_BM = 64, GG_BN = 64, GG_BK = 64, GG_THREADS = 128;
+constexpr int GG_PITCH = GG_BK + 8; // 144-byte rows: the 8 rows of one ldmatrix hit 8 distinct 16-byte bank groups
+
+// byte offsets into one element of the caller's argument array
+// (GroupedGemmMultiABDKernelArgument<1,NumB,NumD>, device_grouped_gemm_multi_abd_fixed_nk.hpp:15-31)
+struct GroupedLayout
+{
+    int stride, off_a, off_b0, off_b1, off_d0, off_e, off_m, off_sa, off_sb0, off_sd0, off_se;
+};
+
+struct GroupedArgs
+{
+    const unsigned char* args;
+    GroupedLayout L;
+    int G, N, K;
+    int has_scale, num_d, d_dtype;
+    int cde_op;
+    uint32_t flags;
+};
+
+template <typename T>
+__device__ __forceinline__ T arg_field(const unsigned char* base, int off)
+{
+    return *reinterpret_cast<const T*>(base + off);
+}
+
+__device__ __forceinline__ void ldmatrix_x4(uint32_t addr, uint32_t* r)
+{
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void ldmatrix_x4_trans(uint32_t addr, uint32_t* r)
+{
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+
+// two int8 codes (bytes i, i+1 of w) times their scales -> packed truncated bf16 pair
+__device__ __forceinline__ uint32_t mul_pair_bf16(uint32_t w, int i, float s0, float s1)
+{
+    const float f0 = float(int(int8_t(w >> (8 * i)))) * s0;       // exact in fp32 (8-bit x 8-bit significands)
+    const float f1 = float(int(int8_t(w >> (8 * (i + 1))))) * s1;
+    return __byte_perm(__float_as_uint(f0), __float_as_uint(f1), 0x7632); // {hi16(f1), hi16(f0)}: truncation
+}
+
+// B_ROW = true : B0[k][n] (mk_kn_mn), shared tile Bs[k][n], fragments through ldmatrix.trans
+// B_ROW = false: B0[n][k] (mk_nk_mn), shared tile Bs[n][k]
+template <bool B_ROW>
+__global__ void __launch_bounds__(GG_THREADS) grouped_gemm_kernel(const GroupedArgs ga)
+{
+    __shared__ __align__(16) uint16_t As[2][GG_BM][GG_PITCH];
+    __shared__ __align__(16) uint16_t Bs[2][GG_BN][GG_PITCH];
+    __shared__ float s_scale[GG_BN];
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int NT = (ga.N + GG_BN - 1) / GG_BN;
+    const int KT = (ga.K + GG_BK - 1) / GG_BK;
+    int buf = 0;
+
+    for(int t = blockIdx.x;; t += gridDim.x)
+    {
+        // ---- locate tile t in the concatenated (group, m-tile, n-tile) list -------------------------------
+        int g = 0, base = 0, Mg = 0;
+        for(; g < ga.G; ++g)
+        {
+            Mg = arg_field<int>(ga.args + size_t(g) * ga.L.stride, ga.L.off_m);
+            const int tiles = ((Mg + GG_BM - 1) / GG_BM) * NT;
+            if(t < base + tiles) break;
+            base += tiles;
+        }
+        if(g >= ga.G) break;
+        const unsigned char* ap = ga.args + size_t(g) * ga.L.stride;
+        const int m0 = ((t - base) / NT) * GG_BM, n0 = ((t - base) % NT) * GG_BN;
+        const uint16_t* A   = arg_field<const uint16_t*>(ap, ga.L.off_a);
+        const int8_t* B     = arg_field<const int8_t*>(ap, ga.L.off_b0);
+        const long long lda = arg_field<int>(ap, ga.L.off_sa), ldb = arg_field<int>(ap, ga.L.off_sb0);
+
+        if(tid < GG_BN)
+        {
+            float s = 1.f;
+            if(ga.has_scale && n0 + tid < ga.N) s = bf16_bits_to_f32(arg_field<const uint16_t*>(ap, ga.L.off_b1)[n0 + tid]);
+            s_scale[tid] = s;
+        }
+
+        uint4 ra[4], rb[2];
+        auto load_regs = [&](int kt) {
+            const int k0 = kt * GG_BK;
+#pragma unroll
+            for(int i = 0; i < 4; ++i)
+            {
+                const int c = tid + i * GG_THREADS, r = c >> 3, kc = (c & 7) * 8;
+                const int m = min(m0 + r, Mg - 1); // rows past M_g repeat the last row; they are never stored
+                ra[i] = (k0 + kc < ga.K) ? *reinterpret_cast<const uint4*>(A + m * lda + k0 + kc) : make_uint4(0, 0, 0, 0);
+            }
+#pragma unroll
+            for(int i = 0; i < 2; ++i)
+            {
+                const int c = tid + i * GG_THREADS, r = c >> 2, cc = (c & 3) * 16;
+                const int k = B_ROW ? k0 + r : k0 + cc, n = B_ROW ? n0 + cc : n0 + r;
+                const bool ok = k < ga.K && n < ga.N;
+                rb[i] = ok ? *reinterpret_cast<const uint4*>(B_ROW ? B + k * ldb + n : B + n * ldb + k) : make_uint4(0, 0, 0, 0);
+            }
+        };
+        auto store_smem = [&](int b) {
+#pragma unroll
+            for(int i = 0; i < 4; ++i)
+            {
+                const int c = tid + i * GG_THREADS, r = c >> 3, kc = (c & 7) * 8;
+                *reinterpret_cast<uint4*>(&As[b][r][kc]) = ra[i];
+            }
+#pragma unroll
+            for(int i = 0; i < 2; ++i)
+            {
+                const int c = tid + i * GG_THREADS, r = c >> 2, cc = (c & 3) * 16;
+                const uint32_t w[4] = {rb[i].x, rb[i].y, rb[i].z, rb[i].w};
+                uint32_t o[8];
+#pragma unroll
+                for(int j = 0; j < 8; ++j)
+                {
+                    // 16 consecutive codes: along n at fixed k (B_ROW: one scale each) or along k at fixed n
+                    const float s0 = B_ROW ? s_scale[cc + 2 * j] : s_scale[r];
+                    const float s1 = B_ROW ? s_scale[cc + 2 * j + 1] : s0;
+                    o[j] = mul_pair_bf16(w[j >> 1], (j & 1) * 2, s0, s1);
+                }
+                *reinterpret_cast<uint4*>(&Bs[b][r][cc])     = make_uint4(o[0], o[1], o[2], o[3]);
+                *reinterpret_cast<uint4*>(&Bs[b][r][cc + 8]) = make_uint4(o[4], o[5], o[6], o[7]);
+            }
+        };
+
+        float acc[8][4];
+#pragma unroll
+        for(int i = 0; i < 8; ++i) acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.f;
+
+        load_regs(0);
+        __syncthreads(); // s_scale visible; every warp is done with the previous tile's buffers
+        for(int kt = 0; kt < KT; ++kt)
+        {
+            store_smem(buf);
+            __syncthreads();
+            if(kt + 1 < KT) load_regs(kt + 1);
+#pragma unroll
+            for(int ks = 0; ks < GG_BK / 16; ++ks)
+            {
+                uint32_t af[4];
+                ldmatrix_x4(ptx::smem_u32(&As[buf][warp * 16 + (lane & 15)][ks * 16 + (lane >> 4) * 8]), af);
+#pragma unroll
+                for(int np = 0; np < 4; ++np)
+                {
+                    uint32_t bf[4]; // {b0,b1} of n8 tile 2np, {b0,b1} of n8 tile 2np+1
+                    if(B_ROW)
+                        ldmatrix_x4_trans(ptx::smem_u32(&Bs[buf][ks * 16 + (lane & 7) + ((lane >> 3) & 1) * 8][np * 16 + (lane >> 4) * 8]), bf);
+                    else
+                        ldmatrix_x4(ptx::smem_u32(&Bs[buf][np * 16 + (lane & 7) + (lane >> 4) * 8][ks * 16 + ((lane >> 3) & 1) * 8]), bf);
+                    ptx::mma_m16n8k16<false>(acc[2 * np], af, bf[0], bf[1]);
+                    ptx::mma_m16n8k16<false>(acc[2 * np + 1], af, bf[2], bf[3]);
+                }
+            }
+            buf ^= 1;
+        }
+
+        // ---- epilogue: CDE functor on the fp32 accumulators, bf16 pairs to E ---------------------------
+        EpiParams ep{};
+        ep.cde_op = ga.cde_op; ep.flags = ga.flags; ep.e_dtype = CKB_BF16; ep.d_dtype[0] = ga.d_dtype;
+        uint16_t* E         = arg_field<uint16_t*>(ap, ga.L.off_e);
+        const long long lde = arg_field<int>(ap, ga.L.off_se);
+        const void* D0      = ga.num_d ? arg_field<const void*>(ap, ga.L.off_d0) : nullptr;
+        const long long ldd = ga.num_d ? arg_field<int>(ap, ga.L.off_sd0) : 0;
+#pragma unroll
+        for(int h = 0; h < 2; ++h)
+        {
+            const int m = m0 + warp * 16 + (lane >> 2) + h * 8;
+            if(m >= Mg) continue;
+#pragma unroll
+            for(int nt = 0; nt < 8; ++nt)
+            {
+                const int n = n0 + nt * 8 + (lane & 3) * 2;
+                if(n >= ga.N) continue; // N is even (checked on the host): n + 1 < N
+                float d0 = 0.f, d1 = 0.f;
+                if(D0)
+                {
+                    d0 = load_d_f32(ga.d_dtype, D0, m * ldd + n);
+                    d1 = load_d_f32(ga.d_dtype, D0, m * ldd + n + 1);
+                }
+                const float v0 = cde_apply_f32(ep, acc[nt][2 * h], d0, 0.f);
+                const float v1 = cde_apply_f32(ep, acc[nt][2 * h + 1], d1, 0.f);
+                *reinterpret_cast<uint32_t*>(E + m * lde + n) =
+                    uint32_t(f32_to_bf16_bits(v0, ga.flags)) | (uint32_t(f32_to_bf16_bits(v1, ga.flags)) << 16);
+            }
+        }
+    }
+}
+
+} // namespace
+
+// Layout of GroupedGemmMultiABDKernelArgument<1, num_b, num_d>: pointers (As, Bs, Ds, E) then index_t fields
+// (M, N, K, StrideAs, StrideBs, StrideDs, StrideE), size rounded up to pointer alignment.
+static GroupedLayout grouped_layout(int num_b, int num_d)
+{
+    GroupedLayout L{};
+    L.off_a   = 0;
+    L.off_b0  = 8;
+    L.off_b1  = num_b > 1 ? 16 : 8;
+    L.off_d0  = 8 * (1 + num_b);
+    L.off_e   = 8 * (1 + num_b + num_d);
+    int o     = L.off_e + 8;
+    L.off_m   = o;
+    L.off_sa  = o + 12;
+    L.off_sb0 = o + 16;
+    L.off_sd0 = o + 16 + 4 * num_b;
+    L.off_se  = o + 16 + 4 * num_b + 4 * num_d;
+    L.stride  = (L.off_se + 4 + 7) & ~7;
+    return L;
+}
+
+int grouped_arg_bytes(int num_b, int num_d) { return grouped_layout(num_b, num_d).stride; }
+
+// IsSupportedArgument of the grouped op: what can be checked from the host-side prototype
+// (device_grouped_gemm_multi_abd_xdl_fixed_nk.hpp:580-610 checks the same things per gemm_desc).
+int check_grouped(const ckb_gemm_problem& p, int group_count)
+{
+    if(group_count <= 0) return set_error(CKB_ERR_UNSUPPORTED, "group_count must be positive");
+    if(p.a_dtype != CKB_BF16 || p.e_dtype != CKB_BF16) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: A and E must be bf16");
+    if(p.a_layout != CKB_ROW) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: A must be row-major (km_* is not built)");
+    if(p.b_dtype != CKB_I8) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: B0 must be int8");
+    if(p.b_layout != CKB_ROW && p.b_layout != CKB_COL) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: B0 must be row- or column-major");
+    if(p.b_op != CKB_BOP_MULTIPLY && p.b_op != CKB_BOP_PASSTHROUGH) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: B op must be Multiply or PassThrough");
+    if(p.b_op == CKB_BOP_MULTIPLY && p.s_dtype != CKB_BF16) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: B1 must be bf16");
+    switch(p.cde_op)
+    {
+    case CKB_CDE_PASSTHROUGH: case CKB_CDE_FASTGELU:
+        if(p.num_d != 0) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: this CDE op takes no D tensor");
+        break;
+    case CKB_CDE_ADD: case CKB_CDE_ADD_FASTGELU: case CKB_CDE_MULTIPLY: case CKB_CDE_MULTIPLY_FASTGELU:
+        if(p.num_d != 1) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: this CDE op takes one D tensor");
+        if(p.d_dtype[0] != CKB_BF16 && p.d_dtype[0] != CKB_F32) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: D0 must be bf16 or fp32");
+        break;
+    default: return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: cde_op %d is not built", p.cde_op);
+    }
+    if(p.N <= 0 || p.K <= 0) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: N and K must be positive");
+    if(p.K % 16 || p.N % 16) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: N and K must be multiples of 16");
+    if(p.lda % 8 || p.lda < p.K) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: StrideA must be >= K and a multiple of 8");
+    const int b_inner = p.b_layout == CKB_ROW ? p.N : p.K;
+    if(p.ldb % 16 || p.ldb < b_inner) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: StrideB0 must cover the row and be a multiple of 16");
+    if(p.lde % 2 || p.lde < p.N) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: StrideE must be >= N and even");
+    return CKB_OK;
+}
+
+int run_grouped(const ckb_gemm_problem& p, const void* dev_args, int group_count, int sum_m, cudaStream_t stream)
+{
+    if(int rc = check_grouped(p, group_count)) return rc;
+    if(!dev_args) return set_error(CKB_ERR_INVALID, "grouped GEMM: the device argument array is null (SetDeviceKernelArgs)");
+    if(sum_m <= 0) return CKB_OK;
+    const int num_b = p.b_op == CKB_BOP_MULTIPLY ? 2 : 1;
+    GroupedArgs ga{};
+    ga.args = static_cast<const unsigned char*>(dev_args);
+    ga.L    = grouped_layout(num_b, p.num_d);
+    ga.G = group_count; ga.N = p.N; ga.K = p.K;
+    ga.has_scale = num_b == 2; ga.num_d = p.num_d; ga.d_dtype = p.d_dtype[0];
+    ga.cde_op = p.cde_op; ga.flags = p.flags;
+    const long long NT    = (p.N + GG_BN - 1) / GG_BN;
+    const long long tiles = ((long long)(sum_m + GG_BM - 1) / GG_BM + group_count) * NT; // upper bound on the tile count
+    const int grid        = int(std::min<long long>(tiles, 6LL * device_info().sm_count));
+    if(p.b_layout == CKB_ROW) grouped_gemm_kernel<true><<<grid, GG_THREADS, 0, stream>>>(ga);
+    else grouped_gemm_kernel<false><<<grid, GG_THREADS, 0, stream>>>(ga);
+    CKB_CUDA_CHECK(cudaGetLastError());
+    return CKB_OK;
+}
+
+} // namespace ckb

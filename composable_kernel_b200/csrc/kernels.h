@@ -43,6 +43,11 @@ int run_wq_gemv(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStream
 int plan_wq_prefill(const ckb_gemm_problem& p, ckb_gemm_plan& plan);
 int run_wq_prefill(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, void* workspace, cudaStream_t stream);
 
+// ---- K4: grouped GEMM, fixed N,K, device-resident argument array ---------------------------------
+int grouped_arg_bytes(int num_b, int num_d);
+int check_grouped(const ckb_gemm_problem& proto, int group_count);
+int run_grouped(const ckb_gemm_problem& proto, const void* dev_args, int group_count, int sum_m, cudaStream_t stream);
+
 // ---- pre-pack ---------------------------------------------------------------------------------
 int launch_prepack_u8(const void* src, void* dst, long long n, cudaStream_t stream);
 int launch_prepack_int4(const void* src, long long sk, long long sn, int N, int K, void* dst, cudaStream_t stream);

@@ -98,3 +98,51 @@ def prepack_u8(w_i8: torch.Tensor) -> torch.Tensor:
     capi.check(capi.lib().ckb_prepack_b_u8(w_i8.data_ptr(), out.data_ptr(), w_i8.numel(),
                                            torch.cuda.current_stream().cuda_stream))
     return out
+
+
+class GroupedGemmOp:
+    """DeviceGroupedGemmMultiABDFixedNK life cycle (client_example/31): G GEMMs sharing N, K and the functors, the
+    per-group pointers / M / strides in a DEVICE array of GroupedGemmMultiABDKernelArgument<1,NumB,NumD> structs
+    (SetDeviceKernelArgs).  as_[i]: bf16 [M_i,K]; b0s[i]: int8, [K,N] (b_layout ROW) or [N,K] (COL); b1s[i]: bf16 [N]
+    or None (PassThrough); d0s[i]: bf16 tensor + its row stride (0 = bias broadcast along M) or None; es[i]: bf16 [M_i,N]."""
+
+    def __init__(self, as_, b0s, b1s, d0s, es, *, b_layout=capi.ROW, cde_op=capi.CDE_PASSTHROUGH, d0_stride=0, flags=0):
+        import struct
+        lib = capi.lib()
+        G = len(as_)
+        num_b = 2 if b1s is not None else 1
+        num_d = 1 if d0s is not None else 0
+        p = capi.GemmProblem()
+        K = as_[0].shape[1]
+        N = es[0].shape[1]
+        p.M, p.N, p.K = sum(a.shape[0] for a in as_), N, K
+        p.a_dtype, p.a_layout, p.lda = _dt(as_[0]), capi.ROW, as_[0].stride(0)
+        p.b_dtype, p.b_layout, p.ldb = _dt(b0s[0]), b_layout, b0s[0].stride(0)
+        p.b_op = capi.BOP_MULTIPLY if num_b == 2 else capi.BOP_PASSTHROUGH
+        if num_b == 2:
+            p.s_dtype = _dt(b1s[0])
+        p.num_d = num_d
+        if num_d:
+            p.d_dtype[0] = _dt(d0s[0])
+        p.cde_op, p.e_dtype, p.lde, p.flags = cde_op, _dt(es[0]), es[0].stride(0), flags
+        self.problem, self.G, self.sum_m = p, G, p.M
+        rc = lib.ckb_grouped_gemm_query(C.byref(p), G)
+        self.supported = rc == 0
+        self.why = capi.last_error() if rc else ""
+        self._keep = (as_, b0s, b1s, d0s, es)
+        stride = int(lib.ckb_grouped_gemm_arg_bytes(num_b, num_d))
+        blob = bytearray()
+        for i in range(G):
+            ptrs = [as_[i].data_ptr(), b0s[i].data_ptr()] + ([b1s[i].data_ptr()] if num_b == 2 else []) + \
+                   ([d0s[i].data_ptr()] if num_d else []) + [es[i].data_ptr()]
+            ints = [as_[i].shape[0], N, K, as_[i].stride(0), b0s[i].stride(0)] + ([0] if num_b == 2 else []) + \
+                   ([d0_stride] if num_d else []) + [es[i].stride(0)]
+            rec = struct.pack(f"<{len(ptrs)}Q{len(ints)}i", *ptrs, *ints)
+            blob += rec + b"\0" * (stride - len(rec))
+        self.dev_args = torch.frombuffer(blob, dtype=torch.uint8).cuda() if G else None
+
+    def run(self, stream=None):
+        if not self.supported:
+            raise capi.CkbError(capi.ERR_UNSUPPORTED, self.why)
+        s = stream if stream is not None else torch.cuda.current_stream().cuda_stream
+        capi.check(capi.lib().ckb_grouped_gemm_run(C.byref(self.problem), self.dev_args.data_ptr(), self.G, self.sum_m, s))

@@ -194,7 +194,20 @@ typedef struct ckb_group_arg { /* mirrors GroupedGemmMultiABDKernelArgument<1,2,
     int32_t stride_a, stride_b0, stride_b1, stride_d0, stride_e;
 } ckb_group_arg;
 
-int ckb_grouped_gemm_run(const ckb_gemm_problem* proto, const ckb_group_arg* dev_args, int32_t group_count,
+/* Size of one element of the device argument array, GroupedGemmMultiABDKernelArgument<1, num_b, num_d>
+   (GetDeviceKernelArgSize / group_count).  ckb_group_arg above is the num_b = 2, num_d = 1 case; with fewer
+   tensors the pointer and stride slots of the missing ones are simply absent, exactly as in the reference struct. */
+uint64_t ckb_grouped_gemm_arg_bytes(int32_t num_b, int32_t num_d);
+
+/* IsSupportedArgument for the grouped op (device_grouped_gemm_multi_abd_xdl_fixed_nk.hpp:580-610).  `proto`
+   carries what the host knows: dtypes, layouts, ops, N, K, the strides (lda, ldb, lde), num_d / d_dtype[0];
+   b_op = MULTIPLY means Bs = (int8 B0, bf16 B1 per channel), PASSTHROUGH means Bs = (B0).  Pointers and M are
+   ignored.  Returns CKB_OK or CKB_ERR_UNSUPPORTED. */
+int ckb_grouped_gemm_query(const ckb_gemm_problem* proto, int32_t group_count);
+
+/* Invoker::Run (:613-676).  `dev_args` = DEVICE array of group_count argument structs (SetDeviceKernelArgs);
+   M of every group is read on the device; sum_m (gemm_descs[i].M_ == sum of all M, :460-463) sizes the grid. */
+int ckb_grouped_gemm_run(const ckb_gemm_problem* proto, const void* dev_args, int32_t group_count,
                          int32_t sum_m, void* stream);
 
 /* ---- misc --------------------------------------------------------------------------------- */

@@ -294,3 +294,67 @@ def test_prefill_fpaintb_cfg1_row_sample():
     ref = o.gemm(a, o.F16, qn.T, o.I8, o.F16, b_op=o.BOP_FPAINTB, scale=np.broadcast_to(s, (K, N)), s_dtype=o.F16)
     bad, err = H.f_close(got, ref, RTOL, ATOL)
     assert bad == 0, f"max err {err}"
+
+
+# ------------------------------------------------------------------------------------------ grouped fixed-NK (client 31)
+@pytest.mark.parametrize("layout,cde,N,K,Ms", [
+    ("row", "add_gelu", 1024, 512, [32 + (7 * i * i) % 32 for i in range(16)]),   # client_example/31 shape
+    ("row", "add", 256, 192, [1, 64, 65, 0, 130]),
+    ("col", "pass", 192, 320, [5, 77]),
+    ("col", "gelu", 128, 64, [64]),
+    ("row", "pass", 80, 48, [3, 9, 200]),                                           # ragged N and K tiles
+    ("col", "add", 80, 48, [17]),
+])
+def test_grouped_fixed_nk_vs_oracle(layout, cde, N, K, Ms):
+    import torch
+    from composable_kernel_b200 import capi, ops
+    o = orc()
+    rng = np.random.default_rng(N + K + len(Ms))
+    cde_c = {"pass": capi.CDE_PASSTHROUGH, "add": capi.CDE_ADD, "gelu": capi.CDE_FASTGELU, "add_gelu": capi.CDE_ADD_FASTGELU}[cde]
+    cde_o = {"pass": o.CDE_PASSTHROUGH, "add": o.CDE_ADD, "gelu": o.CDE_FASTGELU, "add_gelu": o.CDE_ADD_FASTGELU}[cde]
+    hs, devs = [], ([], [], [], [], [])
+    for M in Ms:
+        a = rand_bf16(rng, (M, K))
+        q_kn = rng.integers(-128, 128, (K, N)).astype(np.int8)
+        s = o.bf16_trunc((rng.random(N) * 0.02 + 0.001).astype(np.float32))
+        bias = rand_bf16(rng, (N,))
+        hs.append((a, q_kn, s, bias))
+        devs[0].append(H.to_dev(a, True).reshape(M, K))
+        devs[1].append(H.to_dev(q_kn if layout == "row" else q_kn.T))
+        devs[2].append(H.to_dev(s, True))
+        devs[3].append(H.to_dev(bias, True))
+        devs[4].append(torch.full((M, N), 7.0, dtype=torch.bfloat16, device="cuda"))
+    op = ops.GroupedGemmOp(devs[0], devs[1], devs[2], devs[3] if "add" in cde else None, devs[4],
+                           b_layout=capi.ROW if layout == "row" else capi.COL, cde_op=cde_c, d0_stride=0)
+    assert op.supported, op.why
+    op.run()
+    torch.cuda.synchronize()
+    for (a, q_kn, s, bias), e in zip(hs, devs[4]):
+        M = a.shape[0]
+        if M == 0:
+            continue
+        ds = (np.broadcast_to(bias, (M, N)),) if "add" in cde else ()
+        ref = o.gemm(a, o.BF16, q_kn, o.I8, o.BF16, b_op=o.BOP_MULTIPLY, scale=np.broadcast_to(s, (K, N)), s_dtype=o.BF16,
+                     ds=ds, d_dtypes=(o.BF16,) * len(ds), cde_op=cde_o)
+        bad, err = H.bf16_close(H.from_dev_bf16(e), ref, RTOL, ATOL)
+        assert bad == 0, f"group M={M}: max err {err}"
+
+
+def test_grouped_unsupported_and_null_args():
+    import ctypes as C
+    import torch
+    from composable_kernel_b200 import capi, ops
+    a = [torch.zeros(4, 40, dtype=torch.bfloat16, device="cuda")]
+    b = [torch.zeros(40, 64, dtype=torch.int8, device="cuda")]
+    e = [torch.zeros(4, 64, dtype=torch.bfloat16, device="cuda")]
+    op = ops.GroupedGemmOp(a, b, None, None, e)     # K = 40 is not a multiple of 16
+    assert not op.supported and "multiples of 16" in op.why
+    with pytest.raises(capi.CkbError):
+        op.run()
+    a = [torch.zeros(4, 48, dtype=torch.bfloat16, device="cuda")]
+    b = [torch.zeros(48, 64, dtype=torch.int8, device="cuda")]
+    op = ops.GroupedGemmOp(a, b, None, None, e)
+    assert op.supported
+    # Run without SetDeviceKernelArgs: the reference throws (device_grouped_gemm_multi_abd_xdl_fixed_nk.hpp:597-600)
+    rc = capi.lib().ckb_grouped_gemm_run(C.byref(op.problem), None, 1, 4, None)
+    assert rc == capi.ERR_INVALID
