@@ -8,7 +8,10 @@
 #include <iostream>
 #include <numeric>
 #include <thread>
+#include <string>
 #include <vector>
+
+#include "ck/utility/data_type.hpp"
 
 namespace ck {
 namespace literals {
@@ -123,3 +126,29 @@ struct Tensor
     HostTensorDescriptor mDesc;
     Data mData;
 };
+
+// Print a range converted to T with a delimiter (host_tensor.hpp LogRange / LogRangeAsType in the reference).
+template <typename T, typename Range>
+std::ostream& LogRangeAsType(std::ostream& os, Range&& range, const std::string& delim)
+{
+    bool first = true;
+    for(auto&& v : range)
+    {
+        if(!first) os << delim;
+        first = false;
+        os << ck::type_convert<T>(v);
+    }
+    return os;
+}
+template <typename Range>
+std::ostream& LogRange(std::ostream& os, Range&& range, const std::string& delim)
+{
+    bool first = true;
+    for(auto&& v : range)
+    {
+        if(!first) os << delim;
+        first = false;
+        os << v;
+    }
+    return os;
+}

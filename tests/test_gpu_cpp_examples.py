@@ -20,6 +20,26 @@ CASES = [
     ("example_gemm_quantization_int8", ["3", "1024", "1024", "1024"]),
     ("example_w4a16_group_gemm", ["16", "512", "1024", "1", "0"]),
     ("example_w4a16_group_gemm", ["1", "1024", "512", "0", "0"]),
+    ("client_grouped_gemm_bias_fastgelu_bf16_i8", []),                           # client 31: 16 groups, N=1024, K=512, mk_kn_mn
+    ("client_grouped_gemm_bias_fastgelu_bf16_i8", ["5", "256", "192", "1", "1"]),  # mk_nk_mn
+]
+
+PROFILER = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiler", "bin", "ckProfiler")
+# ckProfiler <op> ...: every factory instance verified against the host reference, then timed (reference test strategy:
+# the op tests are thin wrappers around the profiler's profile_*_impl functions)
+PROFILER_CASES = [
+    ["gemm_multiply_multiply", "3", "1", "1", "2", "0", "1", "512", "768", "640", "-1", "-1", "0", "0", "-1"],
+    ["gemm_multi_abd", "0", "0", "3", "1", "2", "0", "1", "128", "512", "256", "-1", "-1", "-1"],
+    ["gemm_multi_abd", "0", "1", "1", "1", "2", "0", "1", "16", "512", "1024", "-1", "-1", "-1"],
+    ["gemm_multi_abd", "0", "1", "0", "1", "1", "0", "0", "300", "256", "128", "-1", "-1", "-1"],
+    ["gemm_quantization", "0", "1", "2", "0", "1", "256", "512", "384", "0.03"],
+    ["gemm_quantization", "1", "1", "2", "0", "1", "384", "256", "512", "0.01"],
+    ["fpAintB_gemm", "1", "1", "0", "1", "128", "256", "512"],
+    ["fpAintB_gemm", "1", "2", "0", "1", "8", "512", "1024"],
+    ["gemm_w4a16", "1", "2", "0", "1", "4", "1024", "1024", "1"],
+    ["gemm_w4a16", "1", "2", "0", "1", "256", "512", "1024", "0"],
+    ["grouped_gemm_fixed_nk", "0", "0", "1", "2", "0", "1", "40,63,1,130", "512,512,512,512", "256,256,256,256", "-1", "-1", "-1"],
+    ["grouped_gemm_fixed_nk", "0", "1", "1", "1", "0", "1", "17,64", "128,128", "320,320", "-1", "-1", "-1", "1", "2", "5"],
 ]
 
 
@@ -30,3 +50,20 @@ def test_cpp_example(exe, args):
     r = subprocess.run([path] + args, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-2000:])
     assert "PASSED" in r.stdout
+
+
+@pytest.mark.parametrize("args", PROFILER_CASES, ids=["_".join(a[:4]) + f"_{i}" for i, a in enumerate(PROFILER_CASES)])
+def test_ck_profiler(args):
+    assert os.path.exists(PROFILER), f"{PROFILER} not built (run __graft_entry__.build())"
+    r = subprocess.run([PROFILER] + args, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-2000:])
+    assert "verification PASSED" in r.stdout
+    if args[0] != "gemm_multi_abd" or args[7] == "1":
+        assert "Best Perf:" in r.stdout
+
+
+def test_ck_profiler_unknown_operation_and_help():
+    r = subprocess.run([PROFILER, "no_such_op"], capture_output=True, text=True, timeout=60)
+    assert r.returncode != 0 and "cannot find operation" in r.stderr
+    r = subprocess.run([PROFILER], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0 and "gemm_multiply_multiply" in r.stdout and "grouped_gemm_fixed_nk" in r.stdout
