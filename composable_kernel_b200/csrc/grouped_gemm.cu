@@ -17,8 +17,15 @@
 namespace ckb {
 namespace {
 
-constexpr int GG_BM = 64, GG_BN = 64, GG_BK = 64, GG_THREADS = 128;
-constexpr int GG_PITCH = GG_BK + 8; // 144-byte rows: the 8 rows of one ldmatrix hit 8 distinct 16-byte bank groups
+constexpr int GG_BM = 64, GG_BN = 64, GG_BK = 128, GG_THREADS = 256;
+// row pitches (elements) = row + 8: 272- / 144-byte rows, so the 8 rows of one ldmatrix hit 8 distinct 16-byte bank groups
+constexpr int GG_PITCH_K = GG_BK + 8; // As[m][k], Bs[n][k]
+constexpr int GG_PITCH_N = GG_BN + 8; // Bs[k][n] (row-major B)
+constexpr int GG_A_ELEMS = GG_BM * GG_PITCH_K;
+constexpr int GG_B_ELEMS = (GG_BK * GG_PITCH_N > GG_BN * GG_PITCH_K) ? GG_BK * GG_PITCH_N : GG_BN * GG_PITCH_K;
+constexpr int GG_RED_PITCH = GG_BN + 4; // fp32 partial sums [2 k-halves][64][68] = exactly the two A stages
+static_assert(2 * GG_BM * GG_RED_PITCH * 4 <= 2 * GG_A_ELEMS * 2, "reduction area must fit in the A stages");
+constexpr int GG_SMEM    = 2 * (GG_A_ELEMS + GG_B_ELEMS) * 2 + GG_BN * 4;
 
 // byte offsets into one element of the caller's argument array
 // (GroupedGemmMultiABDKernelArgument<1,NumB,NumD>, device_grouped_gemm_multi_abd_fixed_nk.hpp:15-31)
@@ -64,14 +71,19 @@ __device__ __forceinline__ uint32_t mul_pair_bf16(uint32_t w, int i, float s0, f
 
 // B_ROW = true : B0[k][n] (mk_kn_mn), shared tile Bs[k][n], fragments through ldmatrix.trans
 // B_ROW = false: B0[n][k] (mk_nk_mn), shared tile Bs[n][k]
-template <bool B_ROW>
-__global__ void __launch_bounds__(GG_THREADS) grouped_gemm_kernel(const GroupedArgs ga)
+// 8 warps: warp w owns output rows 16*(w&3).. of the 64x64 tile and the k16 steps of half (w>>2) of every 128-k stage;
+// the two k-halves meet in shared memory before the epilogue (an in-CTA split-K: twice the warps per byte in flight).
+template <bool B_ROW, int CDE>
+__global__ void __launch_bounds__(GG_THREADS, 2) grouped_gemm_kernel(const GroupedArgs ga)
 {
-    __shared__ __align__(16) uint16_t As[2][GG_BM][GG_PITCH];
-    __shared__ __align__(16) uint16_t Bs[2][GG_BN][GG_PITCH];
-    __shared__ float s_scale[GG_BN];
+    extern __shared__ __align__(16) unsigned char gg_smem[];
+    uint16_t* const As_base = reinterpret_cast<uint16_t*>(gg_smem);
+    uint16_t* const Bs_base = As_base + 2 * GG_A_ELEMS;
+    float* const s_scale    = reinterpret_cast<float*>(Bs_base + 2 * GG_B_ELEMS);
+    float* const red        = reinterpret_cast<float*>(gg_smem); // [2 k-halves][64][GG_RED_PITCH], aliases the A stages
+    constexpr int BP        = B_ROW ? GG_PITCH_N : GG_PITCH_K;
 
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, wm = warp & 3, wk = warp >> 2;
     const int NT = (ga.N + GG_BN - 1) / GG_BN;
     const int KT = (ga.K + GG_BK - 1) / GG_BK;
     int buf = 0;
@@ -79,13 +91,31 @@ __global__ void __launch_bounds__(GG_THREADS) grouped_gemm_kernel(const GroupedA
     for(int t = blockIdx.x;; t += gridDim.x)
     {
         // ---- locate tile t in the concatenated (group, m-tile, n-tile) list -------------------------------
-        int g = 0, base = 0, Mg = 0;
-        for(; g < ga.G; ++g)
+        // (lane l reads M of group c+l, a warp scan gives the tile prefix: one round trip to L2 per 32 groups
+        //  instead of one per group)
+        int g = ga.G, base = 0, Mg = 0;
+        for(int c = 0; c < ga.G; c += 32)
         {
-            Mg = arg_field<int>(ga.args + size_t(g) * ga.L.stride, ga.L.off_m);
-            const int tiles = ((Mg + GG_BM - 1) / GG_BM) * NT;
-            if(t < base + tiles) break;
-            base += tiles;
+            const int gi  = c + lane;
+            const int Ml  = gi < ga.G ? arg_field<int>(ga.args + size_t(gi) * ga.L.stride, ga.L.off_m) : 0;
+            const int cnt = ((Ml + GG_BM - 1) / GG_BM) * NT;
+            int incl      = cnt;
+#pragma unroll
+            for(int d = 1; d < 32; d <<= 1)
+            {
+                const int v = __shfl_up_sync(0xffffffffu, incl, d);
+                if(lane >= d) incl += v;
+            }
+            const unsigned hit = __ballot_sync(0xffffffffu, gi < ga.G && t < base + incl);
+            if(hit)
+            {
+                const int src = __ffs(hit) - 1;
+                g             = c + src;
+                Mg            = __shfl_sync(0xffffffffu, Ml, src);
+                base += __shfl_sync(0xffffffffu, incl - cnt, src);
+                break;
+            }
+            base += __shfl_sync(0xffffffffu, incl, 31);
         }
         if(g >= ga.G) break;
         const unsigned char* ap = ga.args + size_t(g) * ga.L.stride;
@@ -94,43 +124,47 @@ __global__ void __launch_bounds__(GG_THREADS) grouped_gemm_kernel(const GroupedA
         const int8_t* B     = arg_field<const int8_t*>(ap, ga.L.off_b0);
         const long long lda = arg_field<int>(ap, ga.L.off_sa), ldb = arg_field<int>(ap, ga.L.off_sb0);
 
-        if(tid < GG_BN)
-        {
-            float s = 1.f;
-            if(ga.has_scale && n0 + tid < ga.N) s = bf16_bits_to_f32(arg_field<const uint16_t*>(ap, ga.L.off_b1)[n0 + tid]);
-            s_scale[tid] = s;
-        }
-
         uint4 ra[4], rb[2];
         auto load_regs = [&](int kt) {
             const int k0 = kt * GG_BK;
 #pragma unroll
             for(int i = 0; i < 4; ++i)
             {
-                const int c = tid + i * GG_THREADS, r = c >> 3, kc = (c & 7) * 8;
+                const int c = tid + i * GG_THREADS, r = c >> 4, kc = (c & 15) * 8;
                 const int m = min(m0 + r, Mg - 1); // rows past M_g repeat the last row; they are never stored
                 ra[i] = (k0 + kc < ga.K) ? *reinterpret_cast<const uint4*>(A + m * lda + k0 + kc) : make_uint4(0, 0, 0, 0);
             }
 #pragma unroll
             for(int i = 0; i < 2; ++i)
             {
-                const int c = tid + i * GG_THREADS, r = c >> 2, cc = (c & 3) * 16;
+                const int c = tid + i * GG_THREADS;
+                const int r = B_ROW ? c >> 2 : c >> 3, cc = B_ROW ? (c & 3) * 16 : (c & 7) * 16;
                 const int k = B_ROW ? k0 + r : k0 + cc, n = B_ROW ? n0 + cc : n0 + r;
                 const bool ok = k < ga.K && n < ga.N;
                 rb[i] = ok ? *reinterpret_cast<const uint4*>(B_ROW ? B + k * ldb + n : B + n * ldb + k) : make_uint4(0, 0, 0, 0);
             }
         };
+        load_regs(0); // in flight while the scales arrive
+        if(tid < GG_BN)
+        {
+            float s = 1.f;
+            if(ga.has_scale && n0 + tid < ga.N) s = bf16_bits_to_f32(arg_field<const uint16_t*>(ap, ga.L.off_b1)[n0 + tid]);
+            s_scale[tid] = s;
+        }
         auto store_smem = [&](int b) {
+            uint16_t* As = As_base + b * GG_A_ELEMS;
+            uint16_t* Bs = Bs_base + b * GG_B_ELEMS;
 #pragma unroll
             for(int i = 0; i < 4; ++i)
             {
-                const int c = tid + i * GG_THREADS, r = c >> 3, kc = (c & 7) * 8;
-                *reinterpret_cast<uint4*>(&As[b][r][kc]) = ra[i];
+                const int c = tid + i * GG_THREADS, r = c >> 4, kc = (c & 15) * 8;
+                *reinterpret_cast<uint4*>(As + r * GG_PITCH_K + kc) = ra[i];
             }
 #pragma unroll
             for(int i = 0; i < 2; ++i)
             {
-                const int c = tid + i * GG_THREADS, r = c >> 2, cc = (c & 3) * 16;
+                const int c = tid + i * GG_THREADS;
+                const int r = B_ROW ? c >> 2 : c >> 3, cc = B_ROW ? (c & 3) * 16 : (c & 7) * 16;
                 const uint32_t w[4] = {rb[i].x, rb[i].y, rb[i].z, rb[i].w};
                 uint32_t o[8];
 #pragma unroll
@@ -141,8 +175,8 @@ __global__ void __launch_bounds__(GG_THREADS) grouped_gemm_kernel(const GroupedA
                     const float s1 = B_ROW ? s_scale[cc + 2 * j + 1] : s0;
                     o[j] = mul_pair_bf16(w[j >> 1], (j & 1) * 2, s0, s1);
                 }
-                *reinterpret_cast<uint4*>(&Bs[b][r][cc])     = make_uint4(o[0], o[1], o[2], o[3]);
-                *reinterpret_cast<uint4*>(&Bs[b][r][cc + 8]) = make_uint4(o[4], o[5], o[6], o[7]);
+                *reinterpret_cast<uint4*>(Bs + r * BP + cc)     = make_uint4(o[0], o[1], o[2], o[3]);
+                *reinterpret_cast<uint4*>(Bs + r * BP + cc + 8) = make_uint4(o[4], o[5], o[6], o[7]);
             }
         };
 
@@ -150,26 +184,28 @@ __global__ void __launch_bounds__(GG_THREADS) grouped_gemm_kernel(const GroupedA
 #pragma unroll
         for(int i = 0; i < 8; ++i) acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.f;
 
-        load_regs(0);
-        __syncthreads(); // s_scale visible; every warp is done with the previous tile's buffers
+        __syncthreads(); // s_scale visible; every warp is done with the previous tile's buffers / reduction area
         for(int kt = 0; kt < KT; ++kt)
         {
             store_smem(buf);
             __syncthreads();
             if(kt + 1 < KT) load_regs(kt + 1);
+            const uint16_t* As = As_base + buf * GG_A_ELEMS;
+            const uint16_t* Bs = Bs_base + buf * GG_B_ELEMS;
 #pragma unroll
-            for(int ks = 0; ks < GG_BK / 16; ++ks)
+            for(int kq = 0; kq < GG_BK / 32; ++kq)
             {
+                const int ks = wk * (GG_BK / 32) + kq;
                 uint32_t af[4];
-                ldmatrix_x4(ptx::smem_u32(&As[buf][warp * 16 + (lane & 15)][ks * 16 + (lane >> 4) * 8]), af);
+                ldmatrix_x4(ptx::smem_u32(As + (wm * 16 + (lane & 15)) * GG_PITCH_K + ks * 16 + (lane >> 4) * 8), af);
 #pragma unroll
                 for(int np = 0; np < 4; ++np)
                 {
                     uint32_t bf[4]; // {b0,b1} of n8 tile 2np, {b0,b1} of n8 tile 2np+1
                     if(B_ROW)
-                        ldmatrix_x4_trans(ptx::smem_u32(&Bs[buf][ks * 16 + (lane & 7) + ((lane >> 3) & 1) * 8][np * 16 + (lane >> 4) * 8]), bf);
+                        ldmatrix_x4_trans(ptx::smem_u32(Bs + (ks * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * BP + np * 16 + (lane >> 4) * 8), bf);
                     else
-                        ldmatrix_x4(ptx::smem_u32(&Bs[buf][np * 16 + (lane & 7) + (lane >> 4) * 8][ks * 16 + ((lane >> 3) & 1) * 8]), bf);
+                        ldmatrix_x4(ptx::smem_u32(Bs + (np * 16 + (lane & 7) + (lane >> 4) * 8) * BP + ks * 16 + ((lane >> 3) & 1) * 8), bf);
                     ptx::mma_m16n8k16<false>(acc[2 * np], af, bf[0], bf[1]);
                     ptx::mma_m16n8k16<false>(acc[2 * np + 1], af, bf[2], bf[3]);
                 }
@@ -177,33 +213,61 @@ __global__ void __launch_bounds__(GG_THREADS) grouped_gemm_kernel(const GroupedA
             buf ^= 1;
         }
 
-        // ---- epilogue: CDE functor on the fp32 accumulators, bf16 pairs to E ---------------------------
+        // ---- both k-halves park their fp32 partial sums in shared memory (over the A stages); the epilogue is a
+        //      compact rolled loop: thread -> 8 consecutive columns of one row, sum of the halves, CDE functor,
+        //      one 16-byte store.  (Applying the functor on the MMA fragments unrolls FastGelu's expf + divide 32
+        //      times: ~5600 SASS instructions, and ncu showed the warps starving on instruction fetch.)
+        __syncthreads(); // all MMAs of the last stage are done: the A stages may be overwritten
+        {
+            float* my = red + wk * (GG_BM * GG_RED_PITCH) + (wm * 16 + (lane >> 2)) * GG_RED_PITCH + (lane & 3) * 2;
+#pragma unroll
+            for(int nt = 0; nt < 8; ++nt)
+            {
+                *reinterpret_cast<float2*>(my + nt * 8)                    = make_float2(acc[nt][0], acc[nt][1]);
+                *reinterpret_cast<float2*>(my + 8 * GG_RED_PITCH + nt * 8) = make_float2(acc[nt][2], acc[nt][3]);
+            }
+        }
+        __syncthreads();
         EpiParams ep{};
-        ep.cde_op = ga.cde_op; ep.flags = ga.flags; ep.e_dtype = CKB_BF16; ep.d_dtype[0] = ga.d_dtype;
+        ep.cde_op = CDE; ep.flags = ga.flags; ep.e_dtype = CKB_BF16; ep.d_dtype[0] = CKB_BF16;
         uint16_t* E         = arg_field<uint16_t*>(ap, ga.L.off_e);
         const long long lde = arg_field<int>(ap, ga.L.off_se);
         const void* D0      = ga.num_d ? arg_field<const void*>(ap, ga.L.off_d0) : nullptr;
         const long long ldd = ga.num_d ? arg_field<int>(ap, ga.L.off_sd0) : 0;
-#pragma unroll
-        for(int h = 0; h < 2; ++h)
+#pragma unroll 1
+        for(int c = tid; c < GG_BM * GG_BN / 8; c += GG_THREADS)
         {
-            const int m = m0 + warp * 16 + (lane >> 2) + h * 8;
-            if(m >= Mg) continue;
+            const int r = c >> 3, cc = (c & 7) * 8, m = m0 + r, n = n0 + cc;
+            if(m >= Mg || n >= ga.N) continue; // N % 16 == 0 (host check): the 8 columns are all inside
+            const float* p0 = red + r * GG_RED_PITCH + cc;
+            const float* p1 = p0 + GG_BM * GG_RED_PITCH;
+            float v[8];
 #pragma unroll
-            for(int nt = 0; nt < 8; ++nt)
+            for(int q = 0; q < 8; q += 4)
             {
-                const int n = n0 + nt * 8 + (lane & 3) * 2;
-                if(n >= ga.N) continue; // N is even (checked on the host): n + 1 < N
+                const float4 x = *reinterpret_cast<const float4*>(p0 + q), y = *reinterpret_cast<const float4*>(p1 + q);
+                v[q] = x.x + y.x; v[q + 1] = x.y + y.y; v[q + 2] = x.z + y.z; v[q + 3] = x.w + y.w;
+            }
+            uint32_t o[4];
+#pragma unroll
+            for(int q = 0; q < 8; q += 2)
+            {
                 float d0 = 0.f, d1 = 0.f;
                 if(D0)
                 {
-                    d0 = load_d_f32(ga.d_dtype, D0, m * ldd + n);
-                    d1 = load_d_f32(ga.d_dtype, D0, m * ldd + n + 1);
+                    const long long off = m * ldd + n + q;
+                    if(ga.d_dtype == CKB_F32) { d0 = static_cast<const float*>(D0)[off]; d1 = static_cast<const float*>(D0)[off + 1]; }
+                    else { d0 = bf16_bits_to_f32(static_cast<const uint16_t*>(D0)[off]); d1 = bf16_bits_to_f32(static_cast<const uint16_t*>(D0)[off + 1]); }
                 }
-                const float v0 = cde_apply_f32(ep, acc[nt][2 * h], d0, 0.f);
-                const float v1 = cde_apply_f32(ep, acc[nt][2 * h + 1], d1, 0.f);
-                *reinterpret_cast<uint32_t*>(E + m * lde + n) =
-                    uint32_t(f32_to_bf16_bits(v0, ga.flags)) | (uint32_t(f32_to_bf16_bits(v1, ga.flags)) << 16);
+                const float e0 = cde_apply_f32(ep, v[q], d0, 0.f), e1 = cde_apply_f32(ep, v[q + 1], d1, 0.f);
+                o[q >> 1] = uint32_t(f32_to_bf16_bits(e0, ga.flags)) | (uint32_t(f32_to_bf16_bits(e1, ga.flags)) << 16);
+            }
+            uint16_t* dst = E + m * lde + n;
+            if((reinterpret_cast<uintptr_t>(dst) & 15) == 0) *reinterpret_cast<uint4*>(dst) = make_uint4(o[0], o[1], o[2], o[3]);
+            else
+            {
+#pragma unroll
+                for(int q = 0; q < 4; ++q) *reinterpret_cast<uint32_t*>(dst + 2 * q) = o[q];
             }
         }
     }
@@ -278,9 +342,23 @@ int run_grouped(const ckb_gemm_problem& p, const void* dev_args, int group_count
     ga.cde_op = p.cde_op; ga.flags = p.flags;
     const long long NT    = (p.N + GG_BN - 1) / GG_BN;
     const long long tiles = ((long long)(sum_m + GG_BM - 1) / GG_BM + group_count) * NT; // upper bound on the tile count
-    const int grid        = int(std::min<long long>(tiles, 6LL * device_info().sm_count));
-    if(p.b_layout == CKB_ROW) grouped_gemm_kernel<true><<<grid, GG_THREADS, 0, stream>>>(ga);
-    else grouped_gemm_kernel<false><<<grid, GG_THREADS, 0, stream>>>(ga);
+    const int grid        = int(std::min<long long>(tiles, 3LL * device_info().sm_count));
+    auto go = [&](auto kern) -> int {
+        CKB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GG_SMEM)); // cheap, idempotent
+        kern<<<grid, GG_THREADS, GG_SMEM, stream>>>(ga);
+        return CKB_OK;
+    };
+    const bool row = p.b_layout == CKB_ROW;
+    int rc = CKB_OK;
+    switch(p.cde_op)
+    {
+#define GG_CASE(op) case op: rc = row ? go(grouped_gemm_kernel<true, op>) : go(grouped_gemm_kernel<false, op>); break;
+        GG_CASE(CKB_CDE_PASSTHROUGH) GG_CASE(CKB_CDE_ADD) GG_CASE(CKB_CDE_FASTGELU) GG_CASE(CKB_CDE_ADD_FASTGELU)
+        GG_CASE(CKB_CDE_MULTIPLY) GG_CASE(CKB_CDE_MULTIPLY_FASTGELU)
+#undef GG_CASE
+    default: return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: cde_op %d is not built", p.cde_op);
+    }
+    if(rc) return rc;
     CKB_CUDA_CHECK(cudaGetLastError());
     return CKB_OK;
 }
