@@ -39,6 +39,8 @@ PROFILER_CASES = [
     ["gemm_w4a16", "1", "2", "0", "1", "4", "1024", "1024", "1"],
     ["gemm_w4a16", "1", "2", "0", "1", "256", "512", "1024", "0"],
     ["grouped_gemm_fixed_nk", "0", "0", "1", "2", "0", "1", "40,63,1,130", "512,512,512,512", "256,256,256,256", "-1", "-1", "-1"],
+    ["gemm_universal_reduce", "0", "0", "1", "2", "0", "1", "16", "512", "1024", "-1", "-1", "-1", "4"],     # decode-shaped, KBatch 4
+    ["gemm_universal_reduce", "0", "0", "1", "1", "0", "1", "300", "256", "384", "-1", "-1", "-1", "1"],     # dense path, integer init
     ["grouped_gemm_fixed_nk", "0", "1", "1", "1", "0", "1", "17,64", "128,128", "320,320", "-1", "-1", "-1", "1", "2", "5"],
 ]
 
