@@ -398,6 +398,170 @@ gemm_ss_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// CTA-pair variant (cta_group::2): a cluster of two CTAs on one TPC owns a 256 (M) x 256 (N) tile.  CTA r loads A rows
+// [128r, 128r+128) and B rows (= output columns) [128r, 128r+128) of every k-block into its OWN shared memory -- half
+// the B traffic per SM of the 1-CTA kernel -- and both credit the LEADER's full barrier; the leader's elected thread
+// issues tcgen05.mma.cta_group::2 (M = 256: 128 accumulator lanes in each CTA's TMEM) and multicasts the commits to the
+// barriers of both CTAs.  Each CTA's epilogue warps drain their own 128 rows and release the accumulator on the
+// leader's barrier.  32 KB per stage and CTA -> a 6-stage ring.
+constexpr int SS2_BM       = 256;
+constexpr int SS2_STAGES   = 6;
+constexpr int SS2_HALF     = 128 * SS_BK_BYTES; // one operand half per stage and CTA
+constexpr int SS2_STAGE_BYTES = 2 * SS2_HALF;
+constexpr int SS2_SMEM     = SS2_STAGES * SS2_STAGE_BYTES + 1024 + 256;
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(SS_THREADS, 1)
+gemm_ss2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmBh, const SSArgs args)
+{
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t bar_base  = smem_base + SS2_STAGES * SS2_STAGE_BYTES;
+    auto full_bar   = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar  = [&](int s) { return bar_base + 8u * (SS2_STAGES + s); };
+    auto tfull_bar  = [&](int a) { return bar_base + 8u * (2 * SS2_STAGES + a); };
+    auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * SS2_STAGES + 2 + a); };
+    const uint32_t tmem_slot = bar_base + 8u * (2 * SS2_STAGES + 4);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t rank = ptx::cluster_ctarank();
+    const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+
+    if(warp == 0 && lane == 0)
+    {
+        ptx::prefetch_tmap(&tmA);
+        ptx::prefetch_tmap(&tmBh);
+    }
+    if(warp == 1 && lane == 0)
+    {
+        for(int s = 0; s < SS2_STAGES; ++s)
+        {
+            ptx::mbar_init(full_bar(s), 1);  // used in the leader only: its producer's arrive + both CTAs' bytes
+            ptx::mbar_init(empty_bar(s), 1); // one multicast commit
+        }
+        for(int a = 0; a < 2; ++a)
+        {
+            ptx::mbar_init(tfull_bar(a), 1);
+            ptx::mbar_init(tempty_bar(a), 8); // leader only: 4 epilogue warps of each CTA
+        }
+        ptx::fence_mbar_init();
+    }
+    if(warp == 2)
+    {
+        ptx::tmem_alloc_pair<512>(tmem_slot);
+        ptx::tmem_relinquish_pair();
+    }
+    ptx::tcgen05_fence_before_sync();
+    ptx::cluster_sync(); // barriers of both CTAs are initialised before any remote arrive / multicast commit
+    ptx::tcgen05_fence_after_sync();
+    uint32_t tmem_base;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+    const int num_m_blk = (args.M + SS2_BM - 1) / SS2_BM;
+    const int num_tiles = num_m_blk * args.num_n_blk;
+    const int num_kb    = args.num_kb;
+
+    if(warp == 0)
+    {
+        // ===================== TMA producer (both CTAs) =====================
+        if(lane == 0)
+        {
+            int s = 0;
+            uint32_t ph = 0;
+            for(int t = pair; t < num_tiles; t += num_pairs)
+            {
+                int mb, nb;
+                tile_coord(t, num_m_blk, args.num_n_blk, mb, nb);
+                for(int kb = 0; kb < num_kb; ++kb)
+                {
+                    ptx::mbar_wait(empty_bar(s), ph ^ 1);
+                    if(rank == 0) ptx::mbar_arrive_expect_tx(full_bar(s), 2 * SS2_STAGE_BYTES);
+                    const uint32_t sa = smem_base + s * SS2_STAGE_BYTES;
+                    ptx::tma_load_2d_pair(sa, &tmA, full_bar(s), kb * args.kb_elems, mb * SS2_BM + int(rank) * 128);
+                    ptx::tma_load_2d_pair(sa + SS2_HALF, &tmBh, full_bar(s), kb * args.kb_elems, nb * SS_BN + int(rank) * 128);
+                    if(++s == SS2_STAGES) { s = 0; ph ^= 1; }
+                }
+            }
+        }
+    }
+    else if(warp == 1 && rank == 0)
+    {
+        // ===================== MMA issuer (leader CTA only) =====================
+        int s = 0;
+        uint32_t ph = 0;
+        int as = 0;
+        uint32_t aph = 0;
+        for(int t = pair; t < num_tiles; t += num_pairs)
+        {
+            ptx::mbar_wait(tempty_bar(as), aph ^ 1);
+            ptx::tcgen05_fence_after_sync();
+            const uint32_t d_tmem = tmem_base + as * SS_BN;
+            for(int kb = 0; kb < num_kb; ++kb)
+            {
+                ptx::mbar_wait(full_bar(s), ph);
+                ptx::tcgen05_fence_after_sync();
+                if(lane == 0)
+                {
+                    const uint32_t sa = smem_base + s * SS2_STAGE_BYTES;
+                    const uint64_t da = ptx::make_smem_desc_sw128(sa, 1024);
+                    const uint64_t db = ptx::make_smem_desc_sw128(sa + SS2_HALF, 1024);
+#pragma unroll
+                    for(int j = 0; j < SS_BK_BYTES / 32; ++j)
+                    {
+                        if(args.is_i8)
+                            ptx::mma_i8_ss_pair(d_tmem, da + 2 * j, db + 2 * j, args.idesc, (kb | j) != 0);
+                        else
+                            ptx::mma_f16_ss_pair(d_tmem, da + 2 * j, db + 2 * j, args.idesc, (kb | j) != 0);
+                    }
+                    ptx::mma_commit_pair(empty_bar(s));
+                    if(kb == num_kb - 1) ptx::mma_commit_pair(tfull_bar(as));
+                }
+                __syncwarp();
+                if(++s == SS2_STAGES) { s = 0; ph ^= 1; }
+            }
+            if(++as == 2) { as = 0; aph ^= 1; }
+        }
+    }
+    else if(warp >= 4)
+    {
+        // ===================== epilogue (both CTAs, own 128 rows) =====================
+        const int q = warp & 3;
+        int as = 0;
+        uint32_t aph = 0;
+        for(int t = pair; t < num_tiles; t += num_pairs)
+        {
+            int mb, nb;
+            tile_coord(t, num_m_blk, args.num_n_blk, mb, nb);
+            ptx::mbar_wait(tfull_bar(as), aph);
+            ptx::tcgen05_fence_after_sync();
+            const int m          = mb * SS2_BM + int(rank) * 128 + q * 32 + lane;
+            const uint32_t taddr = tmem_base + as * SS_BN + (uint32_t(q * 32) << 16);
+#pragma unroll 1
+            for(int c = 0; c < SS_BN / 32; ++c)
+            {
+                uint32_t r[32];
+                ptx::tmem_ld_x32(taddr + c * 32, r);
+                ptx::tmem_ld_wait();
+                ss_epilogue_chunk(args, m, nb * SS_BN + c * 32, r);
+            }
+            ptx::tcgen05_fence_before_sync();
+            __syncwarp();
+            if(lane == 0) ptx::mbar_arrive_cluster(ptx::leader_addr(tempty_bar(as)));
+            if(++as == 2) { as = 0; aph ^= 1; }
+        }
+    }
+
+    ptx::tcgen05_fence_before_sync();
+    ptx::cluster_sync(); // neither CTA may leave (or free TMEM) while the other can still touch its barriers / TMEM
+    if(warp == 2)
+    {
+        ptx::tcgen05_fence_after_sync();
+        ptx::tmem_dealloc_pair<512>(tmem_base);
+    }
+}
+
 } // namespace
 
 // ---------------------------------------------------------------------------------------------
@@ -413,14 +577,21 @@ int plan_gemm_ss(const ckb_gemm_problem& p, ckb_gemm_plan& plan)
     const uint32_t box_k = SS_BK_BYTES / eb;
     if(int rc = encode_tmap_2d(&sp->tmA, dt, eb, p.a, p.M, p.K, p.lda, SS_BM, box_k, CU_TENSOR_MAP_SWIZZLE_128B)) return rc;
     if(int rc = encode_tmap_2d(&sp->tmB, dt, eb, p.b, p.N, p.K, p.ldb, SS_BN, box_k, CU_TENSOR_MAP_SWIZZLE_128B)) return rc;
+    if(int rc = encode_tmap_2d(&sp->tmBh, dt, eb, p.b, p.N, p.K, p.ldb, 128, box_k, CU_TENSOR_MAP_SWIZZLE_128B)) return rc;
     const int num_m_blk = (p.M + SS_BM - 1) / SS_BM, num_n_blk = (p.N + SS_BN - 1) / SS_BN;
-    plan.grid       = std::max(1, std::min(device_info().sm_count > 0 ? device_info().sm_count : 148, num_m_blk * num_n_blk));
+    const int sms       = device_info().sm_count > 0 ? device_info().sm_count : 148;
+    // CTA pairs (256x256 tiles) once there are enough pair tiles to fill the machine; CKB_SS_2CTA=0/1 overrides
+    const int pair_tiles = ((p.M + SS2_BM - 1) / SS2_BM) * num_n_blk;
+    sp->pair = p.M >= 2 * SS2_BM && pair_tiles >= sms / 2;
+    if(const char* e = getenv("CKB_SS_2CTA")) sp->pair = atoi(e) != 0;
+    if(sp->pair) plan.grid = 2 * std::max(1, std::min(sms / 2, pair_tiles));
+    else plan.grid = std::max(1, std::min(sms, num_m_blk * num_n_blk));
     plan.block      = SS_THREADS;
-    plan.smem_bytes = SS_SMEM;
+    plan.smem_bytes = sp->pair ? SS2_SMEM : SS_SMEM;
     plan.workspace_bytes = 0;
     plan.split_units     = 1;
-    snprintf(plan.kernel_name, sizeof plan.kernel_name, "gemm_ss_%s_tcgen05_128x256x%d_s%d",
-             i8 ? "i8" : (p.a_dtype == CKB_BF16 ? "bf16" : "f16"), int(box_k), SS_STAGES);
+    snprintf(plan.kernel_name, sizeof plan.kernel_name, sp->pair ? "gemm_ss_%s_tcgen05_2cta_256x256x%d_s%d" : "gemm_ss_%s_tcgen05_128x256x%d_s%d",
+             i8 ? "i8" : (p.a_dtype == CKB_BF16 ? "bf16" : "f16"), int(box_k), sp->pair ? SS2_STAGES : SS_STAGES);
     return CKB_OK;
 }
 
@@ -455,7 +626,17 @@ int run_gemm_ss(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStream
     if(!attr_set)
     {
         CKB_CUDA_CHECK(cudaFuncSetAttribute(gemm_ss_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SS_SMEM));
+        CKB_CUDA_CHECK(cudaFuncSetAttribute(gemm_ss2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SS2_SMEM));
         attr_set = true;
+    }
+    if(sp->pair)
+    {
+        // same instruction descriptor with M = 256 (both CTAs' 128 accumulator lanes); cluster dims are compiled in
+        a.idesc = i8 ? ptx::make_idesc(2, 1, 1, SS2_BM, SS_BN)
+                     : ptx::make_idesc(1, p.a_dtype == CKB_BF16 ? 1 : 0, p.a_dtype == CKB_BF16 ? 1 : 0, SS2_BM, SS_BN);
+        gemm_ss2_kernel<<<plan.grid, SS_THREADS, SS2_SMEM, stream>>>(sp->tmA, sp->tmBh, a);
+        CKB_CUDA_CHECK(cudaGetLastError());
+        return CKB_OK;
     }
     gemm_ss_kernel<<<plan.grid, SS_THREADS, SS_SMEM, stream>>>(sp->tmA, sp->tmB, a);
     CKB_CUDA_CHECK(cudaGetLastError());

@@ -24,6 +24,8 @@ enum KernelId : int32_t {
 struct SSPlan
 {
     CUtensorMap tmA, tmB;
+    CUtensorMap tmBh; // B with a 128-row box: the half of a 256-column tile one CTA of a pair loads
+    int32_t pair;     // 1 = 2-CTA (cta_group::2) kernel, 256x256 tiles per CTA pair
 };
 int plan_gemm_ss(const ckb_gemm_problem& p, ckb_gemm_plan& plan);
 int run_gemm_ss(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStream_t stream);
