@@ -298,11 +298,15 @@ gemm_ss_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int num_tiles = args.num_m_blk * args.num_n_blk;
     const int num_kb    = args.num_kb;
 
-    if(warp == 0)
+    if(warp == 0 || warp == 3)
     {
-        // ===================== TMA producer =====================
+        // ===================== TMA producers =====================
+        // two issuing threads: warp 0 arms the stage and loads A, warp 3 loads B.  One thread needs ~100 ns per TMA
+        // issue, and a k-block is only ~300 ns of MMA work, so a single producer sits right at the issue limit.
+        // (B's bytes may land before A's thread has armed the barrier: its pending arrival keeps the phase open.)
         if(lane == 0)
         {
+            const bool is_a = warp == 0;
             int s = 0;
             uint32_t ph = 0;
             for(int t = blockIdx.x; t < num_tiles; t += gridDim.x)
@@ -312,10 +316,14 @@ gemm_ss_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 for(int kb = 0; kb < num_kb; ++kb)
                 {
                     ptx::mbar_wait(empty_bar(s), ph ^ 1);
-                    ptx::mbar_arrive_expect_tx(full_bar(s), SS_STAGE_BYTES);
                     const uint32_t sa = smem_base + s * SS_STAGE_BYTES;
-                    ptx::tma_load_2d(sa, &tmA, full_bar(s), kb * args.kb_elems, mb * SS_BM);
-                    ptx::tma_load_2d(sa + SS_A_BYTES, &tmB, full_bar(s), kb * args.kb_elems, nb * SS_BN);
+                    if(is_a)
+                    {
+                        ptx::mbar_arrive_expect_tx(full_bar(s), SS_STAGE_BYTES);
+                        ptx::tma_load_2d(sa, &tmA, full_bar(s), kb * args.kb_elems, mb * SS_BM);
+                    }
+                    else
+                        ptx::tma_load_2d(sa + SS_A_BYTES, &tmB, full_bar(s), kb * args.kb_elems, nb * SS_BN);
                     if(++s == SS_STAGES) { s = 0; ph ^= 1; }
                 }
             }
@@ -463,11 +471,12 @@ gemm_ss2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const int num_tiles = num_m_blk * args.num_n_blk;
     const int num_kb    = args.num_kb;
 
-    if(warp == 0)
+    if(warp == 0 || warp == 3)
     {
-        // ===================== TMA producer (both CTAs) =====================
+        // ===================== TMA producers (both CTAs; warp 0 loads A, warp 3 loads B) =====================
         if(lane == 0)
         {
+            const bool is_a = warp == 0;
             int s = 0;
             uint32_t ph = 0;
             for(int t = pair; t < num_tiles; t += num_pairs)
@@ -477,10 +486,14 @@ gemm_ss2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 for(int kb = 0; kb < num_kb; ++kb)
                 {
                     ptx::mbar_wait(empty_bar(s), ph ^ 1);
-                    if(rank == 0) ptx::mbar_arrive_expect_tx(full_bar(s), 2 * SS2_STAGE_BYTES);
                     const uint32_t sa = smem_base + s * SS2_STAGE_BYTES;
-                    ptx::tma_load_2d_pair(sa, &tmA, full_bar(s), kb * args.kb_elems, mb * SS2_BM + int(rank) * 128);
-                    ptx::tma_load_2d_pair(sa + SS2_HALF, &tmBh, full_bar(s), kb * args.kb_elems, nb * SS_BN + int(rank) * 128);
+                    if(is_a)
+                    {
+                        if(rank == 0) ptx::mbar_arrive_expect_tx(full_bar(s), 2 * SS2_STAGE_BYTES);
+                        ptx::tma_load_2d_pair(sa, &tmA, full_bar(s), kb * args.kb_elems, mb * SS2_BM + int(rank) * 128);
+                    }
+                    else
+                        ptx::tma_load_2d_pair(sa + SS2_HALF, &tmBh, full_bar(s), kb * args.kb_elems, nb * SS_BN + int(rank) * 128);
                     if(++s == SS2_STAGES) { s = 0; ph ^= 1; }
                 }
             }
@@ -582,7 +595,8 @@ int plan_gemm_ss(const ckb_gemm_problem& p, ckb_gemm_plan& plan)
     const int sms       = device_info().sm_count > 0 ? device_info().sm_count : 148;
     // CTA pairs (256x256 tiles) once there are enough pair tiles to fill the machine; CKB_SS_2CTA=0/1 overrides
     const int pair_tiles = ((p.M + SS2_BM - 1) / SS2_BM) * num_n_blk;
-    sp->pair = p.M >= 2 * SS2_BM && pair_tiles >= sms / 2;
+    // (measured on B200, tests/ss_pair_probe.py: int8 gains 6-12 % from the pair, bf16/fp16 is level or slower, so 16-bit stays 1-CTA)
+    sp->pair = i8 && p.M >= 2 * SS2_BM && pair_tiles >= sms / 2;
     if(const char* e = getenv("CKB_SS_2CTA")) sp->pair = atoi(e) != 0;
     if(sp->pair) plan.grid = 2 * std::max(1, std::min(sms / 2, pair_tiles));
     else plan.grid = std::max(1, std::min(sms, num_m_blk * num_n_blk));
