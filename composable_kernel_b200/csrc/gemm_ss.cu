@@ -40,15 +40,15 @@ struct SSArgs
     int num_m_blk, num_n_blk;
     uint32_t idesc;
     int is_i8;
+    int band;       // M-blocks per raster band (tile_coord)
     EpiParams ep;
 };
 
-__device__ __forceinline__ void tile_coord(int t, int num_m_blk, int num_n_blk, int& mb, int& nb)
+__device__ __forceinline__ void tile_coord(int t, int num_m_blk, int num_n_blk, int& mb, int& nb, int GROUP = 8)
 {
     // bands of 8 M-blocks; inside a band N-major so concurrently running CTAs share B panels and
     // a band of A stays L2 resident (the role of CK's BlockToCTileMap_Grouped_M00_N0_M01Adapt,
     // grid/block_to_ctile_map.hpp:266-390).
-    constexpr int GROUP = 8;
     const int per_band  = GROUP * num_n_blk;
     const int band      = t / per_band;
     const int first_m   = band * GROUP;
@@ -312,7 +312,7 @@ gemm_ss_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             for(int t = blockIdx.x; t < num_tiles; t += gridDim.x)
             {
                 int mb, nb;
-                tile_coord(t, args.num_m_blk, args.num_n_blk, mb, nb);
+                tile_coord(t, args.num_m_blk, args.num_n_blk, mb, nb, args.band);
                 for(int kb = 0; kb < num_kb; ++kb)
                 {
                     ptx::mbar_wait(empty_bar(s), ph ^ 1);
@@ -377,7 +377,7 @@ gemm_ss_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for(int t = blockIdx.x; t < num_tiles; t += gridDim.x)
         {
             int mb, nb;
-            tile_coord(t, args.num_m_blk, args.num_n_blk, mb, nb);
+            tile_coord(t, args.num_m_blk, args.num_n_blk, mb, nb, args.band);
             ptx::mbar_wait(tfull_bar(as), aph);
             ptx::tcgen05_fence_after_sync();
             const int m          = mb * SS_BM + q * 32 + lane;
@@ -482,7 +482,7 @@ gemm_ss2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             for(int t = pair; t < num_tiles; t += num_pairs)
             {
                 int mb, nb;
-                tile_coord(t, num_m_blk, args.num_n_blk, mb, nb);
+                tile_coord(t, num_m_blk, args.num_n_blk, mb, nb, args.band);
                 for(int kb = 0; kb < num_kb; ++kb)
                 {
                     ptx::mbar_wait(empty_bar(s), ph ^ 1);
@@ -546,7 +546,7 @@ gemm_ss2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         for(int t = pair; t < num_tiles; t += num_pairs)
         {
             int mb, nb;
-            tile_coord(t, num_m_blk, args.num_n_blk, mb, nb);
+            tile_coord(t, num_m_blk, args.num_n_blk, mb, nb, args.band);
             ptx::mbar_wait(tfull_bar(as), aph);
             ptx::tcgen05_fence_after_sync();
             const int m          = mb * SS2_BM + int(rank) * 128 + q * 32 + lane;
@@ -633,6 +633,9 @@ int run_gemm_ss(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStream
     a.num_m_blk = (p.M + SS_BM - 1) / SS_BM;
     a.num_n_blk = (p.N + SS_BN - 1) / SS_BN;
     a.is_i8     = i8;
+    a.band      = 8;
+    if(const char* e = getenv("CKB_SS_BAND")) a.band = std::max(1, atoi(e));
+    if(sp->pair) a.band = std::max(1, a.band / 2); // pair tiles are 256 rows tall
     a.idesc     = i8 ? ptx::make_idesc(2, 1, 1, SS_BM, SS_BN)
                      : ptx::make_idesc(1, p.a_dtype == CKB_BF16 ? 1 : 0, p.a_dtype == CKB_BF16 ? 1 : 0, SS_BM, SS_BN);
     fill_epi(p, a.ep);

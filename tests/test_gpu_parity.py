@@ -83,6 +83,21 @@ def test_int8_accumulators_bit_exact(M, N, K):
     assert np.array_equal(got.astype(np.int64), ref)
 
 
+@pytest.mark.parametrize("M,N,K", [(256, 256, 128), (1, 16, 16), (300, 520, 144), (1000, 520, 2064), (2304, 4864, 256)])
+def test_int8_cta_pair_kernel_bit_exact(M, N, K, monkeypatch):
+    """The cta_group::2 kernel (256x256 tiles per CTA pair) on ragged and multi-tile shapes; the last shape takes it by
+    default (>= 74 pair tiles), the others force it with CKB_SS_2CTA=1."""
+    if (M, N) != (2304, 4864):
+        monkeypatch.setenv("CKB_SS_2CTA", "1")
+    rng = np.random.default_rng(M * 11 + N)
+    a = rng.integers(-128, 128, (M, K)).astype(np.int8)
+    bn = rng.integers(-128, 128, (N, K)).astype(np.int8)
+    got, op = H.run_int8(a, bn, "i32")
+    assert "2cta" in op.kernel_name, op.kernel_name
+    ref = a.astype(np.int64) @ bn.astype(np.int64).T
+    assert np.array_equal(got.astype(np.int64), ref)
+
+
 def test_int8_extreme_values_full_size_k():
     # all operands at -128: |acc| = K * 2^14; K = 8192 -> 2^27, the cfg4 bound
     M, N, K = 128, 256, 8192
