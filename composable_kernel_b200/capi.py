@@ -77,6 +77,7 @@ def lib():
         l.ckb_gemm_host_staging_bytes.argtypes = [C.POINTER(GemmProblem)]
         l.ckb_gemm_host_staging_bytes.restype = C.c_uint64
         l.ckb_gemm_run_host.argtypes = [C.POINTER(GemmProblem), C.c_void_p, C.c_void_p, C.c_void_p]
+        l.ckb_gemm_run_host_async.argtypes = [C.POINTER(GemmProblem), C.c_void_p, C.c_void_p, C.c_void_p]
         l.ckb_prepack_b_u8.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
         l.ckb_prepack_b_rowmajor_i8.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
         l.ckb_prepack_b_int4_bytes.argtypes = [C.c_int32, C.c_int32]
@@ -92,7 +93,7 @@ def lib():
 
 
 EXPORTED = [
-    "ckb_gemm_query", "ckb_gemm_run", "ckb_gemm_host_staging_bytes", "ckb_gemm_run_host",
+    "ckb_gemm_query", "ckb_gemm_run", "ckb_gemm_host_staging_bytes", "ckb_gemm_run_host", "ckb_gemm_run_host_async",
     "ckb_prepack_b_u8", "ckb_prepack_b_rowmajor_i8", "ckb_prepack_b_int4_bytes", "ckb_prepack_b_int4", "ckb_grouped_gemm_run", "ckb_grouped_gemm_query", "ckb_grouped_gemm_arg_bytes",
     "ckb_last_error", "ckb_version", "ckb_device_sm_count",
 ]

@@ -55,6 +55,28 @@ int needed_d(int cde)
 } // namespace
 } // namespace ckb
 
+namespace ckb {
+namespace {
+// Small host->device upload done by SMs reading MAPPED pinned host memory: for the 8-350 KB activation matrices of a
+// decode step a copy-engine transfer costs ~8 us of latency per direction inside the stream, a kernel ~3 us.
+__global__ void __launch_bounds__(256) upload_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, long long n16,
+                                                      const unsigned char* src_tail, unsigned char* dst_tail, int tail)
+{
+    for(long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (long long)gridDim.x * blockDim.x) dst[i] = src[i];
+    if(blockIdx.x == 0 && threadIdx.x < tail) dst_tail[threadIdx.x] = src_tail[threadIdx.x];
+}
+
+// device-visible alias of a pinned (mapped) host pointer, or nullptr when `p` is pageable / not mapped
+void* mapped_alias(const void* p)
+{
+    cudaPointerAttributes at{};
+    if(cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    if(at.type != cudaMemoryTypeHost || !at.devicePointer) return nullptr;
+    return at.devicePointer;
+}
+} // namespace
+} // namespace ckb
+
 using namespace ckb;
 
 extern "C" {
@@ -227,7 +249,7 @@ uint64_t ckb_gemm_host_staging_bytes(const ckb_gemm_problem* p)
     return b;
 }
 
-int ckb_gemm_run_host(const ckb_gemm_problem* pp, void* staging, void* workspace, void* stream)
+static int run_host_impl(const ckb_gemm_problem* pp, void* staging, void* workspace, void* stream, bool sync)
 {
     if(!pp || !staging) return set_error(CKB_ERR_INVALID, "null problem/staging");
     if(pp->M == 0 || pp->N == 0) return CKB_OK;
@@ -236,7 +258,16 @@ int ckb_gemm_run_host(const ckb_gemm_problem* pp, void* staging, void* workspace
     ckb_gemm_problem q = *pp;
     uint8_t* cur = static_cast<uint8_t*>(staging);
     const uint64_t a_bytes = (uint64_t(pp->M - 1) * pp->lda + pp->K) * dtype_bytes(pp->a_dtype);
-    CKB_CUDA_CHECK(cudaMemcpyAsync(cur, pp->a, a_bytes, cudaMemcpyHostToDevice, st));
+    if(void* src = ((reinterpret_cast<uintptr_t>(pp->a) & 15) == 0 && a_bytes <= (4u << 20)) ? mapped_alias(pp->a) : nullptr)
+    {
+        const long long n16 = (long long)(a_bytes / 16);
+        const int blocks    = int(std::min<long long>(device_info().sm_count, (n16 + 255) / 256 + 1));
+        upload_kernel<<<blocks, 256, 0, st>>>(static_cast<const uint4*>(src), reinterpret_cast<uint4*>(cur), n16,
+                                              static_cast<const unsigned char*>(src) + n16 * 16, cur + n16 * 16, int(a_bytes % 16));
+        CKB_CUDA_CHECK(cudaGetLastError());
+    }
+    else
+        CKB_CUDA_CHECK(cudaMemcpyAsync(cur, pp->a, a_bytes, cudaMemcpyHostToDevice, st));
     q.a = cur;
     cur += al(uint64_t(pp->M) * pp->lda * dtype_bytes(pp->a_dtype));
     for(int i = 0; i < pp->num_d; ++i)
@@ -246,15 +277,27 @@ int ckb_gemm_run_host(const ckb_gemm_problem* pp, void* staging, void* workspace
         q.d[i] = cur;
         cur += al(bytes);
     }
-    q.e = cur;
+    // E: the epilogue stores straight into mapped pinned host memory (posted PCIe writes) when it can; otherwise staging + copy
+    void* e_alias = mapped_alias(pp->e);
+    q.e = e_alias ? e_alias : cur;
     ckb_gemm_plan plan;
     if(int rc = ckb_gemm_query(&q, &plan)) return rc;
     if(!plan.supported) return set_error(CKB_ERR_UNSUPPORTED, "%s", last_error().c_str());
     if(int rc = ckb_gemm_run(&q, &plan, workspace, stream)) return rc;
     const uint64_t e_bytes = (uint64_t(pp->M - 1) * pp->lde + pp->N) * dtype_bytes(pp->e_dtype);
-    CKB_CUDA_CHECK(cudaMemcpyAsync(pp->e, cur, e_bytes, cudaMemcpyDeviceToHost, st));
-    CKB_CUDA_CHECK(cudaStreamSynchronize(st));
+    if(!e_alias) CKB_CUDA_CHECK(cudaMemcpyAsync(pp->e, cur, e_bytes, cudaMemcpyDeviceToHost, st));
+    if(sync) CKB_CUDA_CHECK(cudaStreamSynchronize(st));
     return CKB_OK;
+}
+
+int ckb_gemm_run_host(const ckb_gemm_problem* pp, void* staging, void* workspace, void* stream)
+{
+    return run_host_impl(pp, staging, workspace, stream, true);
+}
+
+int ckb_gemm_run_host_async(const ckb_gemm_problem* pp, void* staging, void* workspace, void* stream)
+{
+    return run_host_impl(pp, staging, workspace, stream, false);
 }
 
 int ckb_prepack_b_u8(const void* src, void* dst, int64_t n, void* stream)

@@ -143,6 +143,15 @@ int run_wq_gemv(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStream
     a.zero_const  = p.zero_const;
     a.has_zero    = p.zero != nullptr;
     a.act_rows    = p.M;
+    {
+        // programmatic dependent launch pays inside a CUDA graph (PDL edges: the next kernel's prologue and weight prefill
+        // overlap this one) but an EAGER launch with the attribute costs ~20 us of host time against ~6 us without
+        // (tests/host_cost_probe.py), so it is only requested while the stream is being captured
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        if(cudaStreamIsCapturing(stream, &cs) != cudaSuccess) { cudaGetLastError(); cs = cudaStreamCaptureStatusNone; }
+        a.pdl = cs == cudaStreamCaptureStatusActive;
+        if(const char* e = getenv("CKB_GEMV_PDL")) a.pdl = atoi(e);
+    }
     a.dbg         = getenv("CKB_GEMV_DBG") ? atoi(getenv("CKB_GEMV_DBG")) : 0;
     a.w           = static_cast<const uint8_t*>(p.b);
     a.gtrace      = nullptr;

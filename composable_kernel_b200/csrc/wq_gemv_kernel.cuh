@@ -57,6 +57,7 @@ struct GVArgs
     int zero_const;
     int has_zero;
     int act_rows;   // rows of the activation box (= M)
+    int pdl;        // launch with programmatic stream serialization (0: plain launch)
     int dbg;        // debug knobs (CKB_GEMV_DBG): 1 = skip the math, 2 = weights by 1-D bulk copies
     const uint8_t* w;
     long long* gtrace;
@@ -462,7 +463,7 @@ static int launch_gemv(const GVPlan* gp, const GVArgs& a, int grid, cudaStream_t
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs    = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = a.pdl ? 1 : 0;
     CKB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kfn, gp->tmA, gp->tmW[0], gp->tmW[1], gp->tmS[0], gp->tmS[1], gp->tmZ[0],
                                       gp->tmZ[1], a));
     return CKB_OK;

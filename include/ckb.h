@@ -165,6 +165,10 @@ int ckb_gemm_run(const ckb_gemm_problem* problem, const ckb_gemm_plan* plan, voi
    device->host, synchronises the stream.  `staging` = device scratch of ckb_gemm_host_staging_bytes(). */
 uint64_t ckb_gemm_host_staging_bytes(const ckb_gemm_problem* problem);
 int ckb_gemm_run_host(const ckb_gemm_problem* problem, void* staging, void* workspace, void* stream);
+/* Same, without the final synchronisation: copies and kernel are only ENQUEUED on `stream` (A, D, E must be pinned
+   host memory that stays valid until the caller synchronises).  Calls on one stream may share one staging buffer:
+   stream order keeps GEMM i's E read-back ahead of GEMM i+1's A upload. */
+int ckb_gemm_run_host_async(const ckb_gemm_problem* problem, void* staging, void* workspace, void* stream);
 
 /* ---- weight pre-packing (one-time; excluded from timing exactly as the reference excludes
         UnsignedWeightPreprocessor, example/64_fpAintB_gemm/run_gemm_example.inc:52-58) -------- */

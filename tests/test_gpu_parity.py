@@ -261,6 +261,15 @@ def test_host_buffer_entry_point_matches_device_path():
     capi.check(capi.lib().ckb_gemm_run_host(C.byref(p), staging.data_ptr(), ws,
                                             torch.cuda.current_stream().cuda_stream))
     assert np.array_equal(he.numpy().view(np.uint16), ref)
+    # asynchronous form: three calls share one staging buffer (stream order), one synchronisation at the end
+    hes = [torch.zeros(M, N, dtype=torch.int16).pin_memory() for _ in range(3)]
+    for h in hes:
+        p.e = h.data_ptr()
+        capi.check(capi.lib().ckb_gemm_run_host_async(C.byref(p), staging.data_ptr(), ws,
+                                                      torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    for h in hes:
+        assert np.array_equal(h.numpy().view(np.uint16), ref)
 
 
 # ------------------------------------------------------------------------------------------ prefill-shaped (M > 64)
