@@ -61,11 +61,14 @@ __device__ __forceinline__ void ldmatrix_x4_trans(uint32_t addr, uint32_t* r)
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
 }
 
-// two int8 codes (bytes i, i+1 of w) times their scales -> packed truncated bf16 pair
-__device__ __forceinline__ uint32_t mul_pair_bf16(uint32_t w, int i, float s0, float s1)
+// two int8 codes (bytes i, i+1 of wx = w ^ 0x80808080, i.e. q + 128) times their scales -> packed truncated bf16 pair.
+// 0x4B000000 | (q + 128) is the float 2^23 + q + 128, so one PRMT and one exact FADD give float(q) without the
+// quarter-rate I2F; the product with the bf16 scale is exact in fp32 (8-bit x 8-bit significands).
+template <int I>
+__device__ __forceinline__ uint32_t mul_pair_bf16(uint32_t wx, float s0, float s1)
 {
-    const float f0 = float(int(int8_t(w >> (8 * i)))) * s0;       // exact in fp32 (8-bit x 8-bit significands)
-    const float f1 = float(int(int8_t(w >> (8 * (i + 1))))) * s1;
+    const float f0 = (__uint_as_float(__byte_perm(wx, 0x4B000000u, 0x7540 | I)) - 8388736.f) * s0;
+    const float f1 = (__uint_as_float(__byte_perm(wx, 0x4B000000u, 0x7540 | (I + 1))) - 8388736.f) * s1;
     return __byte_perm(__float_as_uint(f0), __float_as_uint(f1), 0x7632); // {hi16(f1), hi16(f0)}: truncation
 }
 
@@ -165,15 +168,16 @@ __global__ void __launch_bounds__(GG_THREADS, 2) grouped_gemm_kernel(const Group
             {
                 const int c = tid + i * GG_THREADS;
                 const int r = B_ROW ? c >> 2 : c >> 3, cc = B_ROW ? (c & 3) * 16 : (c & 7) * 16;
-                const uint32_t w[4] = {rb[i].x, rb[i].y, rb[i].z, rb[i].w};
+                const uint32_t w[4] = {rb[i].x ^ 0x80808080u, rb[i].y ^ 0x80808080u, rb[i].z ^ 0x80808080u, rb[i].w ^ 0x80808080u};
                 uint32_t o[8];
 #pragma unroll
-                for(int j = 0; j < 8; ++j)
+                for(int j = 0; j < 8; j += 2)
                 {
                     // 16 consecutive codes: along n at fixed k (B_ROW: one scale each) or along k at fixed n
-                    const float s0 = B_ROW ? s_scale[cc + 2 * j] : s_scale[r];
-                    const float s1 = B_ROW ? s_scale[cc + 2 * j + 1] : s0;
-                    o[j] = mul_pair_bf16(w[j >> 1], (j & 1) * 2, s0, s1);
+                    const float s0 = B_ROW ? s_scale[cc + 2 * j] : s_scale[r], s1 = B_ROW ? s_scale[cc + 2 * j + 1] : s0;
+                    const float s2 = B_ROW ? s_scale[cc + 2 * j + 2] : s0, s3 = B_ROW ? s_scale[cc + 2 * j + 3] : s0;
+                    o[j]     = mul_pair_bf16<0>(w[j >> 1], s0, s1);
+                    o[j + 1] = mul_pair_bf16<2>(w[j >> 1], s2, s3);
                 }
                 *reinterpret_cast<uint4*>(Bs + r * BP + cc)     = make_uint4(o[0], o[1], o[2], o[3]);
                 *reinterpret_cast<uint4*>(Bs + r * BP + cc + 8) = make_uint4(o[4], o[5], o[6], o[7]);

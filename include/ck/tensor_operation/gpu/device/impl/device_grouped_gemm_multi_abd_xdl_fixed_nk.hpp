@@ -140,7 +140,7 @@ struct DeviceGroupedGemm_Xdl_Multi_ABD_Fixed_NK
         return std::make_unique<Argument>(p_As, p_Bs, p_Ds, p_Es, gemm_descs, a, b, c);
     }
     std::unique_ptr<BaseInvoker> MakeInvokerPointer() override { return std::make_unique<Invoker>(); }
-    std::string GetTypeString() const override { return "DeviceGroupedGemm_Xdl_Multi_ABD_Fixed_NK<sm_100a, grouped_hmma_64x64x64_persistent>"; }
+    std::string GetTypeString() const override { return "DeviceGroupedGemm_Xdl_Multi_ABD_Fixed_NK<sm_100a, grouped_hmma_64x64x128_8w_persistent>"; }
 
     static void SetElementwiseOps(Argument& arg, AElementwiseOperation a, BElementwiseOperation b, CDEElementwiseOperation c)
     {
