@@ -128,3 +128,29 @@ def test_product_never_imports_the_oracle():
                     if re.search(r"ck_oracle|oracle/|import oracle|from oracle", txt):
                         bad.append(os.path.join(dp, f))
     assert not bad, bad
+
+
+def test_grouped_argument_layout_and_query_without_gpu():
+    """GroupedGemmMultiABDKernelArgument<1,NumB,NumD> sizes (pointers, then index_t fields, padded to 8) and the host-side
+    IsSupportedArgument checks of the grouped op need no device."""
+    import ctypes as C
+    from composable_kernel_b200 import capi
+    lib = capi.lib()
+    assert lib.ckb_grouped_gemm_arg_bytes(2, 1) == 72 == C.sizeof(C.c_void_p) * 5 + 4 * 8
+    assert lib.ckb_grouped_gemm_arg_bytes(2, 0) == 64
+    assert lib.ckb_grouped_gemm_arg_bytes(1, 0) == 48
+    assert lib.ckb_grouped_gemm_arg_bytes(1, 1) == 64
+    assert lib.ckb_grouped_gemm_arg_bytes(3, 0) == 0
+    p = capi.GemmProblem()
+    p.N, p.K, p.lda, p.ldb, p.lde = 1024, 512, 512, 1024, 1024
+    p.a_dtype, p.a_layout, p.b_dtype, p.b_layout, p.e_dtype = capi.BF16, capi.ROW, capi.I8, capi.ROW, capi.BF16
+    p.b_op, p.s_dtype, p.cde_op, p.num_d = capi.BOP_MULTIPLY, capi.BF16, capi.CDE_ADD_FASTGELU, 1
+    p.d_dtype[0] = capi.BF16
+    assert lib.ckb_grouped_gemm_query(C.byref(p), 16) == capi.OK
+    assert lib.ckb_grouped_gemm_query(C.byref(p), 0) == capi.ERR_UNSUPPORTED
+    p.K = 520
+    assert lib.ckb_grouped_gemm_query(C.byref(p), 16) == capi.ERR_UNSUPPORTED and "multiples of 16" in capi.last_error()
+    p.K, p.a_layout = 512, capi.COL
+    assert lib.ckb_grouped_gemm_query(C.byref(p), 16) == capi.ERR_UNSUPPORTED   # km_kn_mn is not built
+    p.a_layout, p.num_d = capi.ROW, 0
+    assert lib.ckb_grouped_gemm_query(C.byref(p), 16) == capi.ERR_UNSUPPORTED   # AddFastGelu needs its D tensor
