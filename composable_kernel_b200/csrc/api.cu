@@ -183,11 +183,23 @@ int ckb_gemm_query(const ckb_gemm_problem* pp, ckb_gemm_plan* plan)
     }
     if(p.b_op == CKB_BOP_GROUP)
     {
-        // W4A16, M <= 64 (larger M with K % 8 != 0: 64-row slabs): N-split HMMA kernel, no workspace
+        // W4A16, M <= 64 (larger M with K % 8 != 0: slabs): N-split HMMA kernels, no workspace.  Two schedules of the same
+        // math (profiles/r2_gemv_variants.txt): the rotating-producer kernel (wq_gemv2, <= 32 rows per launch) wins where one
+        // pass covers the CTA's channels and either M <= 8 or the whole K extent is resident in the ring; the single-producer
+        // kernel (wq_gemv, <= 64 rows) wins on streaming shapes and on M > 8.  CKB_GEMV=1 / 2 forces one of them.
+        const int force = getenv("CKB_GEMV") ? atoi(getenv("CKB_GEMV")) : 0;
+        bool old_kernel = force == 1 || p.M > 32;
+        if(!old_kernel && force != 2)
+        {
+            G2Sched s{};
+            const int sms = device_info().sm_count > 0 ? device_info().sm_count : 148;
+            if(schedule_wq_gemv2(p.M, p.N, p.K, p.zero != nullptr, sms, s) != CKB_OK) old_kernel = true;
+            else old_kernel = !(s.passes == 1 && (s.nt == 1 || s.ring >= s.n_chunks));
+        }
         ckb_gemm_problem q = p;
-        q.M = std::min(p.M, 64);
-        if(int rc = plan_wq_gemv(q, *plan)) { if(rc == CKB_ERR_UNSUPPORTED) { plan->supported = 0; return CKB_OK; } return rc; }
-        plan->kernel_id = KID_WQ_GEMV;
+        q.M = std::min(p.M, old_kernel ? 64 : 32);
+        if(int rc = old_kernel ? plan_wq_gemv(q, *plan) : plan_wq_gemv2(q, *plan)) { if(rc == CKB_ERR_UNSUPPORTED) { plan->supported = 0; return CKB_OK; } return rc; }
+        plan->kernel_id = old_kernel ? KID_WQ_GEMV : KID_WQ_GEMV2;
         plan->supported = 1;
         return CKB_OK;
     }
@@ -214,23 +226,31 @@ int ckb_gemm_run(const ckb_gemm_problem* pp, const ckb_gemm_plan* plan, void* wo
     case KID_GEMM_SS: return run_gemm_ss(*pp, *plan, st);
     case KID_WQ_PREFILL: return run_wq_prefill(*pp, *plan, workspace, st);
     case KID_WQ_GEMV:
+    case KID_WQ_GEMV2:
     case KID_WQ_DECODE: {
-        const bool gemv = plan->kernel_id == KID_WQ_GEMV;
-        if(pp->M <= 64) return gemv ? run_wq_gemv(*pp, *plan, st) : run_wq_decode(*pp, *plan, workspace, st);
-        // slabs of 64 rows; each slab needs its own activation tensor map
-        for(int m0 = 0; m0 < pp->M; m0 += 64)
+        const int kid  = plan->kernel_id;
+        const int slab = kid == KID_WQ_GEMV2 ? 32 : 64; // rows one launch of the kernel handles
+        auto plan_one = [&](const ckb_gemm_problem& q, ckb_gemm_plan& pl) {
+            return kid == KID_WQ_GEMV2 ? plan_wq_gemv2(q, pl) : (kid == KID_WQ_GEMV ? plan_wq_gemv(q, pl) : plan_wq_decode(q, pl));
+        };
+        auto run_one = [&](const ckb_gemm_problem& q, const ckb_gemm_plan& pl) {
+            return kid == KID_WQ_GEMV2 ? run_wq_gemv2(q, pl, st) : (kid == KID_WQ_GEMV ? run_wq_gemv(q, pl, st) : run_wq_decode(q, pl, workspace, st));
+        };
+        if(pp->M <= slab) return run_one(*pp, *plan);
+        // slabs of rows; each slab needs its own activation tensor map
+        for(int m0 = 0; m0 < pp->M; m0 += slab)
         {
             ckb_gemm_problem q = *pp;
-            q.M = std::min(64, pp->M - m0);
+            q.M = std::min(slab, pp->M - m0);
             q.a = static_cast<const uint8_t*>(pp->a) + size_t(m0) * pp->lda * 2;
             q.e = static_cast<uint8_t*>(pp->e) + size_t(m0) * pp->lde * dtype_bytes(pp->e_dtype);
             for(int i = 0; i < pp->num_d; ++i)
                 q.d[i] = static_cast<const uint8_t*>(pp->d[i]) + size_t(m0) * pp->d_sm[i] * dtype_bytes(pp->d_dtype[i]);
             ckb_gemm_plan sub;
             memset(&sub, 0, sizeof sub);
-            if(int rc = gemv ? plan_wq_gemv(q, sub) : plan_wq_decode(q, sub)) return rc;
+            if(int rc = plan_one(q, sub)) return rc;
             sub.supported = 1;
-            if(int rc = gemv ? run_wq_gemv(q, sub, st) : run_wq_decode(q, sub, workspace, st)) return rc;
+            if(int rc = run_one(q, sub)) return rc;
         }
         return CKB_OK;
     }

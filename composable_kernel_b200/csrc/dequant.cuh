@@ -123,6 +123,17 @@ __device__ __forceinline__ void dequant_w4_word_exact2(uint32_t w, uint32_t zm_l
     }
 }
 
+// Same word with the zero point left in: magic + q (128 + q in bf16, 1024 + q in fp16), exact, 3 shifts + 4 lop3.  The caller
+// removes (magic + zp) * sum_k(a_k) from the partial sums (the activation sums come from one extra HMMA per k16 step with an
+// all-ones A fragment, shared by all channel groups of the warp).
+template <bool F16>
+__device__ __forceinline__ void dequant_w4_word_magic(uint32_t w, uint32_t* out4)
+{
+    constexpr uint32_t MAGIC = F16 ? 0x64006400u : 0x43004300u;
+#pragma unroll
+    for(int i = 0; i < 4; ++i) out4[i] = lop3<0xEA>(w >> (4 * i), 0x000F000Fu, MAGIC);
+}
+
 // ---- W8 fpAintB (fp16): u8 -> 0x6400|u8 = 1024 + u8; minus 1152 (= 0x6480) removes the +128 bias
 // (the reference's own trick, unary_element_wise_operation.hpp:1061-1091); times scale: ONE rounding.
 __device__ __forceinline__ void dequant_u8x4_fpaintb(uint32_t w, uint32_t scale2, uint32_t* out2)

@@ -17,7 +17,8 @@ enum KernelId : int32_t {
     KID_GEMM_SS    = 1, // K3: TMA + tcgen05 SS (int8 x int8 -> s32, bf16/f16 dense)
     KID_WQ_DECODE  = 2, // K2: weight-dequant -> TMEM A operand, stream-K, M <= 64
     KID_WQ_PREFILL = 3, // K1: weight dequant pass + dense tcgen05 SS GEMM
-    KID_WQ_GEMV    = 4  // K2 (W4A16): N-split HMMA kernel for M <= 64, no cross-CTA reduction
+    KID_WQ_GEMV    = 4, // round-1 K2 (W4A16): N-split HMMA kernel, CTA-wide stages (kept behind CKB_GEMV=1 for comparison)
+    KID_WQ_GEMV2   = 5  // K2 (W4A16): N-split HMMA kernel for M <= 32 per launch, one TMA pipeline per warp, no cross-CTA reduction
 };
 
 // ---- K3 ---------------------------------------------------------------------------------------
@@ -42,6 +43,15 @@ int plan_wq_decode(const ckb_gemm_problem& p, ckb_gemm_plan& plan);
 int run_wq_decode(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, void* workspace, cudaStream_t stream);
 int plan_wq_gemv(const ckb_gemm_problem& p, ckb_gemm_plan& plan);
 int run_wq_gemv(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStream_t stream);
+// schedule of the W4 decode kernel (host arithmetic only: exercised on CPU through ckb_gemv_schedule)
+struct G2Sched
+{
+    int nt, rb, n_groups, kb_total, grid, passes, n_slots, slot_q, slot_r, g_hi, wn_log2, gw, kbu, upw, n_chunks, ring;
+    int stage_bytes, off_w, off_s, off_z, red_off, bar_off, smem_bytes;
+};
+int schedule_wq_gemv2(int M, int N, int K, bool zp, int sms, G2Sched& s);
+int plan_wq_gemv2(const ckb_gemm_problem& p, ckb_gemm_plan& plan);
+int run_wq_gemv2(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStream_t stream);
 int plan_wq_prefill(const ckb_gemm_problem& p, ckb_gemm_plan& plan);
 int run_wq_prefill(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, void* workspace, cudaStream_t stream);
 

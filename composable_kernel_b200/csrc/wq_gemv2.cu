@@ -1,0 +1,242 @@
+// wq_gemv2.cu -- host side of K2 (W4A16 decode kernel, wq_gemv2_kernel.cuh): slot / ring planning, TMA descriptors, launch.
+#include "wq_gemv2_kernel.cuh"
+
+#include <string>
+#include <vector>
+
+namespace ckb {
+namespace {
+
+int env_int(const char* name, int dflt)
+{
+    const char* e = getenv(name);
+    return e ? atoi(e) : dflt;
+}
+
+} // namespace
+
+int launch_gemv2_f0_nt1(int, int, int, const G2Plan*, const G2Args&, int, cudaStream_t);
+int launch_gemv2_f0_nt2(int, int, int, const G2Plan*, const G2Args&, int, cudaStream_t);
+int launch_gemv2_f0_nt4(int, int, int, const G2Plan*, const G2Args&, int, cudaStream_t);
+int launch_gemv2_f1_nt1(int, int, int, const G2Plan*, const G2Args&, int, cudaStream_t);
+int launch_gemv2_f1_nt2(int, int, int, const G2Plan*, const G2Args&, int, cudaStream_t);
+int launch_gemv2_f1_nt4(int, int, int, const G2Plan*, const G2Args&, int, cudaStream_t);
+
+int launch_gemv2_variant(bool f16, int nt, int gw, int kbu, const G2Plan* gp, const G2Args& a, int grid, cudaStream_t st)
+{
+    if(nt == 1) return f16 ? launch_gemv2_f1_nt1(nt, gw, kbu, gp, a, grid, st) : launch_gemv2_f0_nt1(nt, gw, kbu, gp, a, grid, st);
+    if(nt == 2) return f16 ? launch_gemv2_f1_nt2(nt, gw, kbu, gp, a, grid, st) : launch_gemv2_f0_nt2(nt, gw, kbu, gp, a, grid, st);
+    return f16 ? launch_gemv2_f1_nt4(nt, gw, kbu, gp, a, grid, st) : launch_gemv2_f0_nt4(nt, gw, kbu, gp, a, grid, st);
+}
+
+// Host-side schedule of the decode kernel (also exercised without a GPU by tests/test_capi_cpu.py through
+// ckb_gemv_schedule): how the n16 channel groups and the K range are cut into (CTA, pass, stage, warp) work.
+int schedule_wq_gemv2(int M, int N, int K, bool zp, int sms, G2Sched& s)
+{
+    if(M < 1 || M > 32) return set_error(CKB_ERR_UNSUPPORTED, "W4 decode kernel handles 1 <= M <= 32 per launch");
+    s.nt = M <= 8 ? 1 : (M <= 16 ? 2 : 4);
+    s.rb = s.nt == 1 ? (M <= 1 ? 1 : (M <= 2 ? 2 : (M <= 4 ? 4 : 8))) : 8 * s.nt;
+    const int nw   = g2_warps(s.nt);
+    const int gwmx = g2_gw_max(s.nt);
+    s.n_groups = (N + 15) / 16;
+    s.kb_total = (K + 63) / 64;
+    s.grid     = std::max(1, std::min(sms, s.n_groups));
+    s.grid     = std::max(1, std::min(env_int("CKB_GEMV_GRID", s.grid), s.n_groups));
+    // groups per slot: up to 2 x GW with the warps split into two channel halves (M <= 8), GW otherwise
+    const int gmax    = std::max(1, std::min((s.nt == 1 ? 2 : 1) * gwmx, env_int("CKB_G2_GMAX", 99)));
+    const int per_cta = (s.n_groups + s.grid - 1) / s.grid;
+    s.passes  = (per_cta + gmax - 1) / gmax;
+    s.n_slots = s.grid * s.passes;
+    s.slot_q  = s.n_groups / s.n_slots;
+    s.slot_r  = s.n_groups % s.n_slots;
+    s.g_hi    = s.slot_q + (s.slot_r ? 1 : 0);
+    // 16 warps: all on K (1 x 16) while a warp can hold the slot's groups in <= 64 registers (<= 2), else 2 x 8
+    s.wn_log2 = (s.nt == 1 && s.g_hi > 2) ? 1 : 0;
+    if(s.nt == 1) s.wn_log2 = std::max(0, std::min(1, env_int("CKB_G2_WN", s.wn_log2 + 1) - 1));
+    if((s.g_hi + (1 << s.wn_log2) - 1 >> s.wn_log2) > gwmx) s.wn_log2 = 1;
+    const int wn = 1 << s.wn_log2, wk = nw / wn;
+    s.gw      = (s.g_hi + wn - 1) / wn;
+    const int g_alloc = wn * s.gw; // groups a stage has room for (a warp with gw - 1 groups reads one dead group)
+    auto al = [](int v, int a) { return (v + a - 1) / a * a; };
+    const int red_bytes = nw * s.gw * s.nt * 512;
+    const int bar_bytes = 2 * G2_MAX_RING * 8;
+    // Stage shape: a warp takes `upw` K units of `kbu` 64-k blocks per stage.  Measured (profiles/r2_gemv_stage_shapes.txt):
+    // the per-stage cost (barrier round trip, ~50 instructions per warp) is what hurts, so stages are made as long along K
+    // as the ring allows -- a resident problem (every stage of the CTA fits the ring at once: no refills, no empty
+    // barriers) first, then kbu = 2 (one scale application per 128 k) with >= 2 stages in the 112 KB that keep two CTAs per
+    // SM (the next GEMM of the stream prefetches its weights while this one computes), then the whole SM.
+    int best_kbu = 0, best_upw = 1, best_ring = 0, best_stage = 0, best_score = -1;
+    for(int kbu : {2, 1})
+        for(int upw : {4, 2, 1})
+        {
+            if(int e = env_int("CKB_G2_KBU", 0)) { if(e != kbu) continue; }
+            if(int e = env_int("CKB_G2_UPW", 0)) { if(e != upw) continue; }
+            if(kbu == 1 && upw > 1 && s.rb == 4) continue; // the swizzle phase of the activation rows would depend on the unit
+            const int chk    = wk * upw * kbu, rows = chk / 2;
+            if(chk > 256 || (upw > 1 && wk * (upw / 2) * kbu >= s.kb_total)) continue; // TMA box limit; no point in empty units
+            const int a_b    = al(chk * s.rb * 128, 1024);
+            const int w_b    = g_alloc * chk * 512;
+            const int s_b    = al(rows * 32 * g_alloc + 64, 128);
+            const int z_b    = zp ? al(rows * 16 * g_alloc + 64, 128) : 0;
+            const int stage  = al(a_b + w_b + s_b + z_b, 1024);
+            const int chunks = (s.kb_total + chk - 1) / chk;
+            const int steps  = s.passes * chunks;
+            const int own    = s.passes > 1 ? red_bytes : 0;
+            for(int budget : {112 * 1024, 224 * 1024})
+            {
+                if(int e = env_int("CKB_GEMV_SMEM_KB", 0)) budget = e * 1024;
+                const int ring = std::min({G2_MAX_RING, steps, (budget - bar_bytes - 1024 - own) / stage});
+                if(ring < 1 || (ring < 2 && steps > 1)) continue;
+                if(!own && ring * stage < red_bytes) continue;
+                const bool resident = ring >= steps, two_ctas = budget <= 112 * 1024;
+                const int score = (resident ? 1000 : 0) + (kbu == 2 ? 400 : 0) + (two_ctas ? (resident ? 200 : 20) : 0) + (resident ? 40 : std::min(ring, 4) * 10) +
+                                  (upw == 2 ? 3 : (upw == 4 ? 2 : 0)) * (resident ? 1 : 30);
+                if(score > best_score) { best_score = score; best_kbu = kbu; best_upw = upw; best_ring = ring; best_stage = stage; }
+            }
+        }
+    if(best_kbu == 0) return set_error(CKB_ERR_UNSUPPORTED, "W4 decode kernel: a ring stage does not fit in shared memory");
+    s.kbu = best_kbu; s.upw = best_upw; s.ring = best_ring; s.stage_bytes = best_stage;
+    const int chk = wk * s.upw * s.kbu, rows = chk / 2;
+    s.n_chunks = (s.kb_total + chk - 1) / chk;
+    s.off_w    = al(chk * s.rb * 128, 1024);
+    s.off_s    = s.off_w + g_alloc * chk * 512;
+    s.off_z    = s.off_s + al(rows * 32 * g_alloc + 64, 128);
+    int end    = s.ring * s.stage_bytes;
+    if(s.passes > 1) { s.red_off = end; end += red_bytes; }
+    else s.red_off = 0;
+    s.bar_off    = end;
+    s.smem_bytes = s.bar_off + bar_bytes + 1024;
+    return CKB_OK;
+}
+
+int plan_wq_gemv2(const ckb_gemm_problem& p, ckb_gemm_plan& plan)
+{
+    static_assert(sizeof(G2Plan) <= sizeof(plan.opaque), "opaque too small");
+    G2Plan* gp     = reinterpret_cast<G2Plan*>(plan.opaque);
+    const bool f16 = p.a_dtype == CKB_F16;
+    const bool zp  = p.zero != nullptr;
+    const int sms  = device_info().sm_count > 0 ? device_info().sm_count : 148;
+    G2Sched s{};
+    if(int rc = schedule_wq_gemv2(p.M, p.N, p.K, zp, sms, s)) return rc;
+    gp->nt = s.nt; gp->gw = s.gw; gp->passes = s.passes; gp->slot_q = s.slot_q; gp->slot_r = s.slot_r; gp->g_hi = s.g_hi;
+    gp->wn_log2 = s.wn_log2; gp->kbu = s.kbu; gp->upw = s.upw; gp->n_chunks = s.n_chunks; gp->ring = s.ring; gp->stage_bytes = s.stage_bytes;
+    gp->off_w = s.off_w; gp->off_s = s.off_s; gp->off_z = s.off_z;
+    gp->red_off = s.red_off; gp->bar_off = s.bar_off; gp->smem_bytes = s.smem_bytes; gp->rb = s.rb;
+
+    const int chk = (g2_warps(s.nt) >> s.wn_log2) * s.upw * s.kbu;
+    const CUtensorMapDataType adt = f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    {   // activations as [K/64][M][64]: box = one stage of k-blocks x rb rows x 64 k (rows past M are zero-filled)
+        const uint64_t dims[3] = {64, uint64_t(p.M), uint64_t(s.kb_total)};
+        const uint64_t str[2]  = {uint64_t(p.lda) * 2, 128};
+        const uint32_t box[3]  = {64, uint32_t(s.rb), uint32_t(chk)};
+        if(int rc = encode_tmap_nd(&gp->tmA, adt, 3, p.a, dims, str, box,
+                                   s.rb >= 4 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE)) return rc;
+    }
+    const int kg_total = (p.K + 127) / 128;
+    for(int i = 0; i < 2; ++i)
+    {
+        const int gb = i == 0 ? s.g_hi : std::max(1, s.g_hi - 1);
+        {   // packed weights [n16 group][k64 block][128 words]
+            const uint64_t dims[3] = {128, uint64_t(s.kb_total), uint64_t(s.n_groups)};
+            const uint64_t str[2]  = {512, uint64_t(s.kb_total) * 512};
+            const uint32_t box[3]  = {128, uint32_t(chk), uint32_t(gb)};
+            if(int rc = encode_tmap_nd(&gp->tmW[i], CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, p.b, dims, str, box, CU_TENSOR_MAP_SWIZZLE_NONE)) return rc;
+        }
+        {   // group scales [K/128][N]
+            const uint64_t dims[2] = {uint64_t(p.N), uint64_t(kg_total)};
+            const uint64_t str[1]  = {uint64_t(p.N) * 2};
+            const uint32_t box[2]  = {uint32_t(16 * gb), uint32_t(chk / 2)};
+            if(int rc = encode_tmap_nd(&gp->tmS[i], adt, 2, p.scale, dims, str, box, CU_TENSOR_MAP_SWIZZLE_NONE)) return rc;
+        }
+        if(zp)
+        {
+            const uint64_t dims[2] = {uint64_t(p.N), uint64_t(kg_total)};
+            const uint64_t str[1]  = {uint64_t(p.N)};
+            const uint32_t box[2]  = {uint32_t(16 * gb), uint32_t(chk / 2)};
+            if(int rc = encode_tmap_nd(&gp->tmZ[i], CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, p.zero, dims, str, box, CU_TENSOR_MAP_SWIZZLE_NONE)) return rc;
+        }
+        else
+            gp->tmZ[i] = gp->tmS[i];
+    }
+    plan.grid            = s.grid;
+    plan.block           = g2_threads(s.nt);
+    plan.smem_bytes      = gp->smem_bytes;
+    plan.split_units     = 1;
+    plan.workspace_bytes = 0;
+    snprintf(plan.kernel_name, sizeof plan.kernel_name, "wq_gemv2_w4g128_%s_hmma_%dx%dwarps_g%d_p%d_m%d_u%dx%d_r%d", f16 ? "f16" : "bf16",
+             1 << s.wn_log2, g2_warps(s.nt) >> s.wn_log2, s.gw, s.passes, 8 * s.nt, s.upw, s.kbu, s.ring);
+    return CKB_OK;
+}
+
+int run_wq_gemv2(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStream_t stream)
+{
+    const G2Plan* gp = reinterpret_cast<const G2Plan*>(plan.opaque);
+    G2Args a{};
+    a.M = p.M; a.N = p.N; a.K = p.K;
+    a.kb_total = (p.K + 63) / 64;
+    a.passes   = gp->passes;
+    a.slot_q   = gp->slot_q;
+    a.slot_r   = gp->slot_r;
+    a.g_hi     = gp->g_hi;
+    a.wn_log2  = gp->wn_log2;
+    a.upw      = gp->upw;
+    a.n_chunks = gp->n_chunks;
+    a.ring     = gp->ring;
+    a.stage_bytes = gp->stage_bytes;
+    a.off_w = gp->off_w; a.off_s = gp->off_s; a.off_z = gp->off_z;
+    a.red_off    = gp->red_off;
+    a.bar_off    = gp->bar_off;
+    a.rb         = gp->rb;
+    a.zero_const = p.zero_const;
+    a.has_zero   = p.zero != nullptr;
+    {
+        // programmatic dependent launch pays inside a CUDA graph (PDL edges: the next kernel's prologue and weight prefill
+        // overlap this one) but an EAGER launch with the attribute costs ~20 us of host time against ~6 us without
+        // (tests/host_cost_probe.py), so it is only requested while the stream is being captured
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        if(cudaStreamIsCapturing(stream, &cs) != cudaSuccess) { cudaGetLastError(); cs = cudaStreamCaptureStatusNone; }
+        a.pdl = cs == cudaStreamCaptureStatusActive;
+        a.pdl = env_int("CKB_GEMV_PDL", a.pdl);
+    }
+    a.dbg   = env_int("CKB_GEMV_DBG", 0);
+    a.trace = nullptr;
+    fill_epi_params(p, a.ep);
+#ifdef CKB_ENABLE_TRACE
+    if(const char* tf = getenv("CKB_G2_TRACE"))
+    {
+        // debug: per-warp timeline of up to 64 consecutive launches (each launch gets its own region, so a captured graph
+        // records the steady state under programmatic dependent launch); dumped at process exit
+        static constexpr int MAXL = 64, PER = 160 * 16 * 10;
+        static long long* buf = nullptr;
+        static int n_launch = 0;
+        static int grids[MAXL];
+        static std::string path;
+        if(!buf)
+        {
+            cudaMalloc(&buf, size_t(MAXL) * PER * 8);
+            cudaMemset(buf, 0, size_t(MAXL) * PER * 8);
+            path = tf;
+            atexit([] {
+                cudaDeviceSynchronize();
+                std::vector<long long> h(size_t(MAXL) * PER);
+                cudaMemcpy(h.data(), buf, h.size() * 8, cudaMemcpyDeviceToHost);
+                if(FILE* f = fopen(path.c_str(), "w"))
+                {
+                    for(int l = 0; l < std::min(n_launch, MAXL); ++l)
+                        for(int c = 0; c < grids[l] * 16; ++c)
+                        {
+                            fprintf(f, "%d %d %d", l, c / 16, c % 16);
+                            for(int k = 0; k < 10; ++k) fprintf(f, " %lld", h[size_t(l) * PER + c * 10 + k]);
+                            fprintf(f, "\n");
+                        }
+                    fclose(f);
+                }
+            });
+        }
+        if(n_launch < MAXL && plan.grid <= 160) { a.trace = buf + size_t(n_launch) * PER; grids[n_launch] = plan.grid; ++n_launch; }
+    }
+#endif
+    return launch_gemv2_variant(p.a_dtype == CKB_F16, gp->nt, gp->gw, gp->kbu, gp, a, plan.grid, stream);
+}
+
+} // namespace ckb

@@ -1,0 +1,36 @@
+// wq_gemv2_inst.cu -- explicit instantiations of the W4A16 decode kernel (wq_gemv2_kernel.cuh), one translation unit per
+// (activation type, token-tile count): built six times with -DGV_INST_F16={0,1} -DGV_INST_NT={1,2,4}.
+#include "wq_gemv2_kernel.cuh"
+
+#ifndef GV_INST_F16
+#error "compile with -DGV_INST_F16=0|1 -DGV_INST_NT=1|2|4"
+#endif
+
+namespace ckb {
+
+#define GV_JOIN2(a, b) a##b
+#define GV_JOIN(a, b) GV_JOIN2(a, b)
+#define GV_FN GV_JOIN(GV_JOIN(launch_gemv2_f, GV_INST_F16), GV_JOIN(_nt, GV_INST_NT))
+
+int GV_FN(int nt, int gw, int kbu, const G2Plan* gp, const G2Args& a, int grid, cudaStream_t st)
+{
+    constexpr bool F16 = GV_INST_F16 != 0;
+    const bool zp      = a.has_zero != 0;
+#define GV_CASE(NT_, GW_)                                                                                                    \
+    if(nt == NT_ && gw == GW_)                                                                                               \
+    {                                                                                                                        \
+        if(kbu == 2) return zp ? launch_gemv2<NT_, GW_, 2, F16, true>(gp, a, grid, st) : launch_gemv2<NT_, GW_, 2, F16, false>(gp, a, grid, st); \
+        return zp ? launch_gemv2<NT_, GW_, 1, F16, true>(gp, a, grid, st) : launch_gemv2<NT_, GW_, 1, F16, false>(gp, a, grid, st); \
+    }
+#if GV_INST_NT == 1
+    GV_CASE(1, 1) GV_CASE(1, 2) GV_CASE(1, 3) GV_CASE(1, 4)
+#elif GV_INST_NT == 2
+    GV_CASE(2, 1) GV_CASE(2, 2) GV_CASE(2, 3) GV_CASE(2, 4)
+#else
+    GV_CASE(4, 1) GV_CASE(4, 2)
+#endif
+#undef GV_CASE
+    return set_error(CKB_ERR_INVALID, "no W4 decode kernel variant for nt %d gw %d", nt, gw);
+}
+
+} // namespace ckb

@@ -11,6 +11,13 @@ from composable_kernel_b200 import capi, ops  # noqa: E402
 
 
 def timeit(ops_list, iters=20):
+    if os.environ.get("PERF_ONCE"):
+        # three eager launches of the first operand set (for an ncu capture: the third one is warm)
+        s = torch.cuda.current_stream().cuda_stream
+        for _ in range(3):
+            ops_list[0].run(s)
+        torch.cuda.synchronize()
+        return float("nan")
     if os.environ.get("PERF_GRAPH"):
         # CUDA-graph replay of the whole rotation (launch overhead of the host API taken out)
         st = torch.cuda.Stream()
