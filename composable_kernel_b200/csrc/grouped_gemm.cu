@@ -9,6 +9,8 @@
 // (binary_element_wise_operation.hpp:184-190: bf16( float(int8) * float(bf16 scale) ), truncating) on its way
 // into shared memory, fragments come from ldmatrix, products accumulate in fp32 registers (HMMA m16n8k16).
 // The client-31 problem (16 groups x ~48 rows x 1024 x 512) is ~10 MB / 0.8 GFLOP: launch- and HBM-bound.
+#include <array>
+#include <cstddef>
 #include "common.cuh"
 #include "epilogue.cuh"
 #include "kernels.h"
@@ -279,24 +281,56 @@ __global__ void __launch_bounds__(GG_THREADS, 2) grouped_gemm_kernel(const Group
 
 } // namespace
 
-// Layout of GroupedGemmMultiABDKernelArgument<1, num_b, num_d>: pointers (As, Bs, Ds, E) then index_t fields
-// (M, N, K, StrideAs, StrideBs, StrideDs, StrideE), size rounded up to pointer alignment.
+// Layout of GroupedGemmMultiABDKernelArgument<1, num_b, num_d> (device_grouped_gemm_multi_abd_fixed_nk.hpp:15-31 of the
+// reference): taken with offsetof from a mirror of the struct, because a zero-length std::array member still occupies
+// storage (one byte, then padding) -- the offsets of a NumDTensor == 0 instantiation are NOT "NumD * 8 bytes fewer".
+namespace {
+template <int NB, int ND>
+struct KernelArgMirror
+{
+    std::array<const void*, 1> p_as_grid;
+    std::array<const void*, NB> p_bs_grid;
+    std::array<const void*, ND> p_ds_grid;
+    void* p_e_grid;
+    int M, N, K;
+    std::array<int, 1> StrideAs;
+    std::array<int, NB> StrideBs;
+    std::array<int, ND> StrideDs;
+    int StrideE;
+};
+template <int NB, int ND>
+GroupedLayout layout_of()
+{
+    using T = KernelArgMirror<NB, ND>;
+    GroupedLayout L{};
+    L.off_a   = int(offsetof(T, p_as_grid));
+    L.off_b0  = int(offsetof(T, p_bs_grid));
+    L.off_b1  = NB > 1 ? L.off_b0 + 8 : L.off_b0;
+    L.off_d0  = int(offsetof(T, p_ds_grid));
+    L.off_e   = int(offsetof(T, p_e_grid));
+    L.off_m   = int(offsetof(T, M));
+    L.off_sa  = int(offsetof(T, StrideAs));
+    L.off_sb0 = int(offsetof(T, StrideBs));
+    L.off_sd0 = int(offsetof(T, StrideDs));
+    L.off_se  = int(offsetof(T, StrideE));
+    L.stride  = int(sizeof(T));
+    return L;
+}
+// the instantiations the reference's grouped bf16 x int8 instances use (NumB 1|2, NumD 0|1), as the host compiler lays them out
+using KA21 = KernelArgMirror<2, 1>;
+using KA20 = KernelArgMirror<2, 0>;
+using KA11 = KernelArgMirror<1, 1>;
+using KA10 = KernelArgMirror<1, 0>;
+static_assert(sizeof(KA21) == 72 && offsetof(KA21, p_e_grid) == 32 && offsetof(KA21, StrideE) == 68, "NumB 2, NumD 1");
+static_assert(sizeof(KA20) == 72 && offsetof(KA20, p_e_grid) == 32 && offsetof(KA20, M) == 40 && offsetof(KA20, StrideE) == 68, "NumB 2, NumD 0");
+static_assert(sizeof(KA10) == 64 && offsetof(KA10, p_e_grid) == 24 && offsetof(KA10, StrideE) == 56, "NumB 1, NumD 0");
+static_assert(sizeof(KA11) == 64 && offsetof(KA11, p_e_grid) == 24, "NumB 1, NumD 1");
+} // namespace
+
 static GroupedLayout grouped_layout(int num_b, int num_d)
 {
-    GroupedLayout L{};
-    L.off_a   = 0;
-    L.off_b0  = 8;
-    L.off_b1  = num_b > 1 ? 16 : 8;
-    L.off_d0  = 8 * (1 + num_b);
-    L.off_e   = 8 * (1 + num_b + num_d);
-    int o     = L.off_e + 8;
-    L.off_m   = o;
-    L.off_sa  = o + 12;
-    L.off_sb0 = o + 16;
-    L.off_sd0 = o + 16 + 4 * num_b;
-    L.off_se  = o + 16 + 4 * num_b + 4 * num_d;
-    L.stride  = (L.off_se + 4 + 7) & ~7;
-    return L;
+    if(num_b == 2) return num_d ? layout_of<2, 1>() : layout_of<2, 0>();
+    return num_d ? layout_of<1, 1>() : layout_of<1, 0>();
 }
 
 int grouped_arg_bytes(int num_b, int num_d) { return grouped_layout(num_b, num_d).stride; }
