@@ -175,9 +175,11 @@ int ckb_gemm_query(const ckb_gemm_problem* pp, ckb_gemm_plan* plan)
     if(!device_info().ok) { plan->supported = 0; return set_error(CKB_ERR_NO_DEVICE, "no sm_100 device"); }
     if(p.M > 64 && p.K % 8 == 0)
     {
-        // prefill-shaped: expand the weight once, then the dense tcgen05 GEMM with the fused epilogue
-        if(int rc = plan_wq_prefill(p, *plan)) return rc;
-        plan->kernel_id = KID_WQ_PREFILL;
+        // prefill-shaped: the fused TMA -> dequant -> tcgen05 pair kernel (no workspace).  CKB_PREFILL_TWO_PASS=1 selects the
+        // round-1 form (expand the weight into the workspace, then the dense GEMM) for comparison.
+        const bool two_pass = getenv("CKB_PREFILL_TWO_PASS") && atoi(getenv("CKB_PREFILL_TWO_PASS")) == 1;
+        if(int rc = two_pass ? plan_wq_prefill(p, *plan) : plan_wq_fused(p, *plan)) return rc;
+        plan->kernel_id = two_pass ? KID_WQ_PREFILL : KID_WQ_FUSED;
         plan->supported = 1;
         return CKB_OK;
     }
@@ -225,6 +227,7 @@ int ckb_gemm_run(const ckb_gemm_problem* pp, const ckb_gemm_plan* plan, void* wo
     {
     case KID_GEMM_SS: return run_gemm_ss(*pp, *plan, st);
     case KID_WQ_PREFILL: return run_wq_prefill(*pp, *plan, workspace, st);
+    case KID_WQ_FUSED: return run_wq_fused(*pp, *plan, st);
     case KID_WQ_GEMV:
     case KID_WQ_GEMV2:
     case KID_WQ_DECODE: {

@@ -189,4 +189,119 @@ store_row_f32(const EpiParams& ep, int m, int n0, const float* v)
     }
 }
 
+// D(m, n0..n0+31) as fp32.  Fast paths: per-column vector (d_sm == 0, d_sn == 1: bias / column scale, 16-byte loads),
+// per-row scalar (d_sn == 0: row scale); anything else element by element.
+__device__ __forceinline__ void load_d_chunk32(const EpiParams& ep, int i, int m, int n0, float* d)
+{
+    const int dt = ep.d_dtype[i];
+    const long long sm = ep.d_sm[i], sn = ep.d_sn[i];
+    const char* base = static_cast<const char*>(ep.d[i]);
+    if(sn == 0)
+    {
+        const float v = load_d_f32(dt, base, (long long)m * sm);
+#pragma unroll
+        for(int j = 0; j < 32; ++j) d[j] = v;
+        return;
+    }
+    const bool full = (n0 + 32 <= ep.N);
+    if(sn == 1 && full && (dt == CKB_BF16 || dt == CKB_F16))
+    {
+        const uint16_t* p = reinterpret_cast<const uint16_t*>(base) + (long long)m * sm + n0;
+        if((reinterpret_cast<uintptr_t>(p) & 15) == 0)
+        {
+#pragma unroll
+            for(int j = 0; j < 4; ++j)
+            {
+                const uint4 q = __ldg(reinterpret_cast<const uint4*>(p) + j);
+                const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+                for(int t = 0; t < 4; ++t)
+                {
+                    if(dt == CKB_BF16)
+                    {
+                        d[8 * j + 2 * t]     = __uint_as_float(w[t] << 16);
+                        d[8 * j + 2 * t + 1] = __uint_as_float(w[t] & 0xffff0000u);
+                    }
+                    else
+                    {
+                        const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[t]));
+                        d[8 * j + 2 * t] = f.x; d[8 * j + 2 * t + 1] = f.y;
+                    }
+                }
+            }
+            return;
+        }
+    }
+    if(sn == 1 && full && (dt == CKB_F32 || dt == CKB_I32))
+    {
+        const uint32_t* p = reinterpret_cast<const uint32_t*>(base) + (long long)m * sm + n0;
+        if((reinterpret_cast<uintptr_t>(p) & 15) == 0)
+        {
+#pragma unroll
+            for(int j = 0; j < 8; ++j)
+            {
+                const uint4 q = __ldg(reinterpret_cast<const uint4*>(p) + j);
+                const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+                for(int t = 0; t < 4; ++t) d[4 * j + t] = dt == CKB_F32 ? __uint_as_float(w[t]) : float(int32_t(w[t]));
+            }
+            return;
+        }
+    }
+#pragma unroll
+    for(int j = 0; j < 32; ++j) d[j] = (n0 + j < ep.N) ? load_d_f32(dt, base, (long long)m * sm + (long long)(n0 + j) * sn) : 0.f;
+}
+
+// One accumulator row chunk (32 fp32 columns of row m, bit patterns in r) through the float CDE functors.  The functor is
+// selected ONCE per chunk so the element loops are branch-free.
+__device__ __forceinline__ void cde_chunk32_f32(const EpiParams& ep, int m, int n0, const uint32_t* r, float* v)
+{
+    float d0[32], d1[32];
+    if(ep.num_d > 0) load_d_chunk32(ep, 0, m, n0, d0);
+    if(ep.num_d > 1) load_d_chunk32(ep, 1, m, n0, d1);
+    const bool half_arith = ep.e_dtype == CKB_F16 && ep.num_d > 0 && ep.d_dtype[0] == CKB_F16;
+    switch(ep.cde_op)
+    {
+    case CKB_CDE_ADD:
+#pragma unroll
+        for(int i = 0; i < 32; ++i)
+            v[i] = half_arith ? __half2float(__hadd(__float2half_rn(__uint_as_float(r[i])), __float2half_rn(d0[i])))
+                              : __uint_as_float(r[i]) + d0[i];
+        break;
+    case CKB_CDE_FASTGELU:
+#pragma unroll
+        for(int i = 0; i < 32; ++i) v[i] = fast_gelu_f32(__uint_as_float(r[i]));
+        break;
+    case CKB_CDE_ADD_FASTGELU:
+#pragma unroll
+        for(int i = 0; i < 32; ++i) v[i] = fast_gelu_f32(__uint_as_float(r[i]) + d0[i]);
+        break;
+    case CKB_CDE_MULTIPLY:
+#pragma unroll
+        for(int i = 0; i < 32; ++i)
+            v[i] = half_arith ? __half2float(__hmul(__float2half_rn(__uint_as_float(r[i])), __float2half_rn(d0[i])))
+                              : __uint_as_float(r[i]) * d0[i];
+        break;
+    case CKB_CDE_MULTIPLY_ADD:
+#pragma unroll
+        for(int i = 0; i < 32; ++i) v[i] = __fadd_rn(__fmul_rn(__uint_as_float(r[i]), d0[i]), d1[i]);
+        break;
+    case CKB_CDE_MULTIPLY_FASTGELU:
+#pragma unroll
+        for(int i = 0; i < 32; ++i) v[i] = fast_gelu_f32(__uint_as_float(r[i]) * d0[i]);
+        break;
+    case CKB_CDE_MULTIPLY_ADD_FASTGELU:
+#pragma unroll
+        for(int i = 0; i < 32; ++i) v[i] = fast_gelu_f32(__fadd_rn(__fmul_rn(__uint_as_float(r[i]), d0[i]), d1[i]));
+        break;
+    case CKB_CDE_MULTIPLY_MULTIPLY:
+#pragma unroll
+        for(int i = 0; i < 32; ++i) v[i] = __fmul_rn(__fmul_rn(__uint_as_float(r[i]), d0[i]), d1[i]);
+        break;
+    default:
+#pragma unroll
+        for(int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+    }
+}
+
 } // namespace ckb

@@ -18,7 +18,8 @@ enum KernelId : int32_t {
     KID_WQ_DECODE  = 2, // K2: weight-dequant -> TMEM A operand, stream-K, M <= 64
     KID_WQ_PREFILL = 3, // K1: weight dequant pass + dense tcgen05 SS GEMM
     KID_WQ_GEMV    = 4, // round-1 K2 (W4A16): N-split HMMA kernel, CTA-wide stages (kept behind CKB_GEMV=1 for comparison)
-    KID_WQ_GEMV2   = 5  // K2 (W4A16): N-split HMMA kernel for M <= 32 per launch, one TMA pipeline per warp, no cross-CTA reduction
+    KID_WQ_GEMV2   = 5, // K2 (W4A16): N-split HMMA kernel for M <= 32 per launch, rotating producer, no cross-CTA reduction
+    KID_WQ_FUSED   = 6  // K1: fused TMA -> dequant -> tcgen05 cta_group::2 prefill kernel (no workspace)
 };
 
 // ---- K3 ---------------------------------------------------------------------------------------
@@ -39,6 +40,8 @@ struct WQPlan
     int32_t n_mma;     // MMA N (padded M tile)
     int32_t units_total, units_per_tile;
 };
+int plan_wq_fused(const ckb_gemm_problem& p, ckb_gemm_plan& plan);
+int run_wq_fused(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStream_t stream);
 int plan_wq_decode(const ckb_gemm_problem& p, ckb_gemm_plan& plan);
 int run_wq_decode(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, void* workspace, cudaStream_t stream);
 int plan_wq_gemv(const ckb_gemm_problem& p, ckb_gemm_plan& plan);

@@ -460,6 +460,14 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_cluster_addr)
 {
     asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar_cluster_addr) : "memory");
 }
+// Same arrive with the default semantics (.release at CTA scope), as CUTLASS's ClusterBarrier::arrive does for a remote
+// barrier: .release.cluster compiles to MEMBAR.ALL.GPU + ERRBAR in front of the SYNCS.ARRIVE (ncu: the membar stall was the
+// longest link of the transform chain of the fused prefill kernel).  Correct where the data the barrier guards was made
+// visible by other means -- fence.proxy.async for operand stages read by the tensor core, tcgen05 fences for TMEM.
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t bar_cluster_addr)
+{
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar_cluster_addr) : "memory");
+}
 // tile load into THIS CTA's shared memory, completion bytes credited to the LEADER CTA's barrier
 __device__ __forceinline__ void tma_load_2d_pair(uint32_t smem_dst, const CUtensorMap* m, uint32_t bar, int32_t x, int32_t y)
 {
