@@ -6,7 +6,14 @@ One STEP = one decode pass over all 32 layers' weight GEMMs at each M in {1,4,16
   -> 224 GEMMs per M, 672 launches per step, every GEMM on its own layer's weights (3.4 GB of packed
   int4 + scales per rank: far larger than the 126 MB L2, so no flush is needed between iterations).
 metric = algorithmic HBM GB/s (A + packed B + scales + E bytes per GEMM) over
-all launches; TFLOP/s and per-shape numbers ride along in "detail".
+all launches; TFLOP/s and per-shape numbers ride along in "detail" (every entry timed under CUDA-graph replay).
+The other half of BASELINE.json's metric rides on the same JSON line:
+  "prefill"  W4A16 g128 at M=4096 on (11008,4096), (4096,11008), (28672,8192): TFLOP/s and its own tensor-bound roofline;
+  "configs"  BASELINE.json configs: cfg1 fpAintB 3840x4096x4096, cfg3 bf16 x int8 Multiply + bias 4096x14336x4096,
+             cfg4 int8 8192^3 MultiplyMultiply (against a cuBLASLt int8 peak measured in the same run), cfg5 28672x8192 at
+             M in {1,16,4096};
+  "cfg5_sharded" (N > 1): ONE global N=28672 weight column-sharded over the ranks (strong scaling), with and without the
+             all-gather of the E slices.
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--no-graph]
 """
@@ -42,6 +49,39 @@ def peaks():
             d = json.load(f)
         return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def tensor_peaks():
+    """dense bf16 TFLOP/s: (burst, sustained, source)."""
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return float(d["bf16_tflops"]), float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), "measured (MEASURED_PEAKS.json)"
+    return 1650.0, 1400.0, "fallback (B200_PROFILING.md)"
+
+
+def time_graph(torch, ops_list, reps=3, stream=None):
+    """us per launch of `ops_list` replayed `reps` times as ONE CUDA graph (programmatic dependent launch between the
+    decode kernels, no host launch cost) -- the same way the headline step is timed."""
+    st = stream or torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        for op in ops_list:
+            op.run(st.cuda_stream)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=st):
+            for op in ops_list:
+                op.run(st.cuda_stream)
+        g.replay()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(st)
+        for _ in range(reps):
+            g.replay()
+        b.record(st)
+        torch.cuda.synchronize()
+    return a.elapsed_time(b) * 1e3 / (reps * len(ops_list))
 
 
 class ClockSampler:
@@ -131,6 +171,7 @@ def main():
     ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of replaying a CUDA graph")
     ap.add_argument("--layers", type=int, default=LAYERS)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the prefill / BASELINE-config blocks (headline only)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -224,25 +265,16 @@ def main():
         ms_total = ev0.elapsed_time(ev1)
         clk = clocks.stop() if rank == 0 else None
 
-        # per-shape detail (eager back-to-back launches of one op family, its own events)
-        detail = {}
+        # per-shape detail: every (M, shape) family replayed as its own CUDA graph over all layers' weights (> L2)
+        detail = {"launch": "cuda-graph replay (same as the headline step)"}
         if rank == 0:
             for M in MS:
                 for (N, K) in sorted(set(LAYER_SHAPES)):
                     sel = [op for op in gemm_ops if op.problem.M == M and op.problem.N == N and op.problem.K == K]
-                    s = torch.cuda.current_stream().cuda_stream
-                    for op in sel:
-                        op.run(s)
-                    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                    a.record()
-                    for _ in range(3):
-                        for op in sel:
-                            op.run(s)
-                    b.record()
-                    torch.cuda.synchronize()
-                    us = a.elapsed_time(b) * 1e3 / (3 * len(sel))
+                    us = time_graph(torch, sel, 3, stream)
                     detail[f"M{M}_N{N}_K{K}"] = {"us": round(us, 3), "gbps": round(algo_bytes(M, N, K) / us / 1e3, 1),
-                                                 "tflops": round(2 * M * N * K / us / 1e6, 3)}
+                                                 "frac_hbm": round(algo_bytes(M, N, K) / us / 1e3 / peaks()[0], 4),
+                                                 "tflops": round(2 * M * N * K / us / 1e6, 3), "kernel": sel[0].kernel_name}
 
     t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
     if world > 1:
@@ -256,68 +288,92 @@ def main():
     if rank == 0 or world > 1:
         import ctypes as C
         lib = capi.lib()
+        NS = 4  # streams the independent GEMMs of a step are spread over (each with its own staging buffer)
         host_a = {k: v.cpu().pin_memory() for k, v in acts.items()}
-        host_e = {k: torch.zeros_like(v, device="cpu").pin_memory() for k, v in outs.items()}
-        staging = torch.empty(1 << 20, dtype=torch.uint8, device=dev)
-        probs = []
+        streams = [torch.cuda.Stream(device=dev) for _ in range(NS)]
+        stagings = [torch.empty(1 << 20, dtype=torch.uint8, device=dev) for _ in range(NS)]
+        probs, host_e = [], []
         h2d = d2h = 0
-        for op in gemm_ops:
+        for i, op in enumerate(gemm_ops):
             p = capi.GemmProblem()
             C.memmove(C.byref(p), C.byref(op.problem), C.sizeof(p))
+            he = torch.zeros(p.M, p.N, dtype=torch.bfloat16).pin_memory()  # every GEMM of the step owns its result buffer
+            host_e.append(he)
             p.a = host_a[(p.M, p.K)].data_ptr()
-            p.e = host_e[(p.M, p.N)].data_ptr()
-            probs.append((p, op.workspace.data_ptr() if op.workspace is not None else None))
+            p.e = he.data_ptr()
+            probs.append((p, op.workspace.data_ptr() if op.workspace is not None else None, i % NS))
             h2d += 2 * p.M * p.K
             d2h += 2 * p.M * p.N
-        s = torch.cuda.current_stream().cuda_stream
-        e2e_steps = max(1, min(args.steps, 3))
+        e2e_steps = max(10, min(args.steps, 20))
+
+        def enqueue(strs):
+            for p, ws, k in probs:
+                capi.check(lib.ckb_gemm_run_host_async(C.byref(p), stagings[k].data_ptr(), ws, strs[k].cuda_stream))
 
         def e2e_step():
-            # every GEMM: A from pinned host memory -> device, kernel, E -> pinned host memory, all enqueued on one
-            # stream (stream order protects the shared staging buffer); ONE synchronisation ends the step, when the
-            # caller owns all 672 results
-            for p, ws in probs:
-                capi.check(lib.ckb_gemm_run_host_async(C.byref(p), staging.data_ptr(), ws, s))
+            # every GEMM: A from pinned host memory -> device, kernel, E -> pinned host memory; the GEMMs of a step are
+            # independent, so they are enqueued round-robin on NS streams (stream order protects each staging buffer) and
+            # ONE device synchronisation ends the step, when the caller owns all 672 results.  The plan of each distinct
+            # problem is cached inside the library.
+            enqueue(streams)
             torch.cuda.synchronize()
-        e2e_step()
+        for _ in range(2):
+            e2e_step()
         barrier()
         t0 = time.perf_counter()
         for _ in range(e2e_steps):
             e2e_step()
         torch.cuda.synchronize()
         dt = (time.perf_counter() - t0) / e2e_steps
-        tt = torch.tensor([dt], dtype=torch.float64, device=dev)
+        # the same chain of C-ABI calls captured once and replayed as a CUDA graph (the copies are graph nodes: still inside
+        # the timed region, every step moves the same bytes)
+        dt_graph = None
+        try:
+            st2 = torch.cuda.Stream(device=dev)
+            side = [torch.cuda.Stream(device=dev) for _ in range(NS)]
+            with torch.cuda.stream(st2):
+                g2 = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g2, stream=st2):
+                    for sd in side:
+                        sd.wait_stream(st2)
+                    enqueue(side)
+                    for sd in side:
+                        st2.wait_stream(sd)
+                g2.replay()
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                for _ in range(e2e_steps):
+                    g2.replay()
+                    torch.cuda.synchronize()
+                dt_graph = (time.perf_counter() - t0) / e2e_steps
+        except Exception as e:  # noqa: BLE001
+            print(f"# e2e graph capture failed: {e}", file=sys.stderr)
+            torch.cuda.synchronize()
+        tt = torch.tensor([dt, dt_graph if dt_graph is not None else dt], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        e2e = {"value": world * step_bytes / float(tt.item()) / 1e9, "unit": "GB/s",
-               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": float(tt.item()) * 1e3,
-               "note": "ckb_gemm_run_host_async per GEMM: pinned-host A -> device, kernel, E -> pinned host, one stream sync per step; "
-                       "weights stay device-resident (the reference also uploads weights once, outside timing)"}
+        dt, dtg = float(tt[0].item()), float(tt[1].item())
+        best = min(dt, dtg)
+        e2e = {"value": world * step_bytes / best / 1e9, "unit": "GB/s", "mode": "graph_replay" if dtg < dt else "eager_calls",
+               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": best * 1e3, "steps": e2e_steps,
+               "eager_calls": {"value": world * step_bytes / dt / 1e9, "ms_per_step": dt * 1e3},
+               "graph_replay": None if dt_graph is None else {"value": world * step_bytes / dtg / 1e9, "ms_per_step": dtg * 1e3},
+               "copies_declared": True,
+               "note": "every step moves A of every GEMM from pinned host memory to the device and E of every GEMM back to pinned host "
+                       "memory through ckb_gemm_run_host_async (GEMMs round-robin on 4 streams, one device sync per step, plans cached "
+                       "in the library). eager_calls: the C-ABI is called per GEMM every step; graph_replay: the same call chain "
+                       "captured once into a CUDA graph (copies are graph nodes) and replayed per step; value = the faster of the two. "
+                       "Weights stay device-resident (the reference also uploads weights once, outside timing)"}
 
-    # ---- N-sharded path with the output all-gather (NCCL over NVLink), timed separately ----------------
-    with_gather = None
+    # ---- the other half of the metric (rank 0, single-GPU runs): prefill M=4096 and the BASELINE configs ----------------
+    prefill = configs = None
+    if world == 1 and not args.no_extras:
+        prefill, configs = extras(torch, capi, ops, dev)
+
+    # ---- cfg5 column-sharded over the ranks (strong scaling), with and without the E all-gather ----------------------
+    sharded = None
     if world > 1:
-        from composable_kernel_b200 import shard
-        sel = gemm_ops[::8]  # bounded sample of the step's GEMM list (every 8th launch)
-        def gather_step():
-            s_ = torch.cuda.current_stream().cuda_stream
-            for op in sel:
-                op.run(s_)
-                shard.all_gather_columns(outs[(op.problem.M, op.problem.N)], world, row_major=False)
-        gather_step()
-        barrier()
-        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        g0.record()
-        for _ in range(3):
-            gather_step()
-        g1.record()
-        barrier()
-        tg = torch.tensor([g0.elapsed_time(g1) / 3], dtype=torch.float64, device=dev)
-        dist.all_reduce(tg, op=dist.ReduceOp.MAX)
-        sel_bytes = sum(algo_bytes(op.problem.M, op.problem.N, op.problem.K) for op in sel)
-        with_gather = {"value": world * sel_bytes / (float(tg.item()) * 1e-3) / 1e9, "unit": "GB/s",
-                       "sample": f"every 8th GEMM of the step ({len(sel)} launches), eager, all_gather_into_tensor of "
-                                 "each E slice into E_all[G][M][N/G] after every GEMM"}
+        sharded = cfg5_sharded(torch, dist, capi, ops, dev, rank, world)
 
     if rank == 0:
         peak, peak_src = peaks()
@@ -326,11 +382,16 @@ def main():
         cpu = None
         if not args.no_cpu_baseline:
             cpu = cpu_baseline()
-        traffic = None  # dram bytes per launch from the committed ncu --set full capture (ratio x algorithmic bytes)
-        tp = os.path.join(ROOT, "profiles", "r1_traffic.json")
-        if os.path.exists(tp):
-            with open(tp) as f:
-                traffic = json.load(f)["traffic_over_algorithmic"] * step_bytes / launches_per_step
+        # DRAM bytes per launch cannot be measured inside this run (it needs a profiler): the committed ncu --set full capture of
+        # the same kernels gives dram__bytes / algorithmic bytes, applied here to this run's algorithmic bytes -- labelled as such
+        traffic, traffic_src = None, None
+        for name in ("r2_traffic.json", "r1_traffic.json"):
+            tp = os.path.join(ROOT, "profiles", name)
+            if os.path.exists(tp):
+                with open(tp) as f:
+                    traffic = json.load(f)["traffic_over_algorithmic"] * step_bytes / launches_per_step
+                traffic_src = f"profiles/{name} (ncu dram__bytes_read+write of these kernels / algorithmic bytes) x this run's algorithmic bytes; not measured live"
+                break
         line = {
             "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
@@ -339,16 +400,19 @@ def main():
                                    "((4096,4096)x4,(11008,4096)x2,(4096,11008)x1)",
                        "launch": "cuda-graph replay" if graph is not None else "eager",
                        "l2": "inputs larger than L2 (3.4 GB of distinct weights per step)",
-                       "parallelism": f"column-shard x{world}: every rank owns an N-shard of the shapes above "
-                                      "(independent shards, no collective in the GEMM; all-gather reported in with_allgather)"},
+                       "parallelism": f"x{world} independent replicas of the GEMM list, one per GPU, own weights, no collective (weak scaling); "
+                                      "the N-sharded strong-scaling measurement of one global weight is the cfg5_sharded block"},
             "tflops": world * step_flops / (ms_per_step * 1e-3) / 1e12,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": traffic, "algorithmic_bytes_per_launch": step_bytes / launches_per_step,
+                         "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "algorithmic_bytes_per_launch": step_bytes / launches_per_step,
                          "peak_source": peak_src,
-                         "kernel": gemm_ops[0].kernel_name, "us_per_launch": us_per_launch},
+                         "kernel": gemm_ops[0].kernel_name, "kernels": sorted({op.kernel_name for op in gemm_ops}),
+                         "us_per_launch": us_per_launch},
             "cpu_baseline": cpu,
             "e2e": e2e,
-            "with_allgather": with_gather,
+            "prefill": prefill,
+            "configs": configs,
+            "cfg5_sharded": sharded,
             "gpu_launches": launches_per_step * args.steps,
             "clocks": clk,
             "detail": detail,
@@ -356,6 +420,202 @@ def main():
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def _rot(nbytes_per_set, target=300e6, cap=6):
+    """operand sets to rotate through so that consecutive launches never find their weights in the 126 MB L2"""
+    return int(max(2, min(cap, target // max(1, nbytes_per_set) + 1)))
+
+
+def extras(torch, capi, ops, dev):
+    """Prefill M=4096 (W4A16 g128) and the BASELINE.json configs, each timed as a CUDA graph over rotating operand sets."""
+    burst, sustained, src = tensor_peaks()
+    hbm = peaks()[0]
+    lib = capi.lib()
+
+    def w4_ops(M, N, K, nrot=None):
+        nrot = nrot or _rot(N * K // 2)
+        a = torch.randn(M, K, device=dev).bfloat16()
+        lst = []
+        for _ in range(nrot):
+            packed = torch.randint(0, 256, (int(lib.ckb_prepack_b_int4_bytes(N, K)),), dtype=torch.uint8, device=dev)
+            sc = (torch.rand(K // GROUP, N, device=dev) * 0.015 + 0.005).bfloat16()
+            e = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+            op = ops.GemmOp(a, packed, e, b_dtype=capi.I4, b_layout=capi.PREPACKED, b_op=capi.BOP_GROUP, N=N, K=K, scale=sc,
+                            zero_const=8, group_size=GROUP)
+            assert op.supported, op.why
+            lst.append(op)
+        return lst
+
+    def entry(us, M, N, K, nbytes, kernel, tensor=True):
+        tf = 2 * M * N * K / us / 1e6
+        d = {"us": round(us, 2), "tflops": round(tf, 2), "gbps": round(nbytes / us / 1e3, 1), "kernel": kernel}
+        if tensor:
+            d["frac_bf16_burst"] = round(tf / burst, 4)
+            d["frac_bf16_sustained"] = round(tf / sustained, 4)
+        else:
+            d["frac_hbm"] = round(nbytes / us / 1e3 / hbm, 4)
+        return d
+
+    prefill = {"dtype": "bf16 A x int4 g128 B, fp32 accumulate", "M": 4096, "launch": "cuda-graph replay, rotating weight sets > L2",
+               "peak_source": src, "shapes": {}}
+    best = None
+    for (N, K) in [(11008, 4096), (4096, 11008), (28672, 8192)]:
+        lst = w4_ops(4096, N, K)
+        us = time_graph(torch, lst, 3)
+        prefill["shapes"][f"N{N}_K{K}"] = entry(us, 4096, N, K, algo_bytes(4096, N, K), lst[0].kernel_name)
+        tf = 2 * 4096 * N * K / us / 1e6
+        if best is None or N == 28672:
+            best = (tf, lst[0].kernel_name, us)
+        del lst
+        torch.cuda.empty_cache()
+    prefill["roofline"] = {"bound": "tensor", "achieved": round(best[0], 2), "peak": burst, "unit": "TFLOP/s",
+                           "frac": round(best[0] / burst, 4), "frac_sustained": round(best[0] / sustained, 4),
+                           "kernel": best[1], "shape": "M4096_N28672_K8192", "us_per_launch": round(best[2], 2), "traffic": None}
+
+    configs = {}
+    # cfg1: example/64_fpAintB_gemm default problem 3840 x 4096 x 4096, fp16 A x biased-u8 B, per-channel fp16 scale
+    M, N, K = 3840, 4096, 4096
+    a = torch.randn(M, K, device=dev).half()
+    lst = []
+    for _ in range(_rot(N * K)):
+        b = ops.prepack_u8(torch.randint(-128, 128, (N, K), dtype=torch.int8, device=dev))
+        sc = (torch.rand(N, device=dev) * 0.02 + 0.001).half()
+        e = torch.empty(M, N, dtype=torch.float16, device=dev)
+        lst.append(ops.GemmOp(a, b, e, b_op=capi.BOP_FPAINTB, scale=sc))
+    us = time_graph(torch, lst, 3)
+    configs["cfg1_fpAintB_fp16_i8_3840x4096x4096"] = entry(us, M, N, K, 2 * M * K + N * K + 2 * N + 2 * M * N, lst[0].kernel_name)
+    del lst
+    # cfg3: client_example/30 bf16 A x int8 B (Multiply by a bf16 scale) + bias, 4096 x 14336 x 4096
+    M, N, K = 4096, 14336, 4096
+    a = torch.randn(M, K, device=dev).bfloat16()
+    lst = []
+    for _ in range(_rot(N * K)):
+        b = torch.randint(-128, 128, (N, K), dtype=torch.int8, device=dev)
+        sc = (torch.rand(N, device=dev) * 0.01).bfloat16()
+        bias = torch.randn(N, device=dev).bfloat16()
+        e = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+        lst.append(ops.GemmOp(a, b, e, b_op=capi.BOP_MULTIPLY, scale=sc, ds=(bias,), d_strides=((0, 1),), cde_op=capi.CDE_ADD))
+    us = time_graph(torch, lst, 3)
+    configs["cfg3_bf16_i8_multiply_bias_4096x14336x4096"] = entry(us, M, N, K, 2 * M * K + N * K + 4 * N + 2 * M * N, lst[0].kernel_name)
+    del lst
+    torch.cuda.empty_cache()
+    # cfg4: example/65 int8 x int8 -> int32, MultiplyMultiply (column scale x row scale) -> bf16, 8192^3
+    M = N = K = 8192
+    lst = []
+    for _ in range(3):
+        a8 = torch.randint(-128, 128, (M, K), dtype=torch.int8, device=dev)
+        b8 = torch.randint(-128, 128, (N, K), dtype=torch.int8, device=dev)
+        d0 = torch.rand(N, device=dev) * 1e-3
+        d1 = torch.rand(M, device=dev) * 1e-3
+        e = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
+        lst.append(ops.GemmOp(a8, b8, e, ds=(d0, d1), d_strides=((0, 1), (1, 0)), cde_op=capi.CDE_MULTIPLY_MULTIPLY))
+    us = time_graph(torch, lst, 3)
+    c4 = {"us": round(us, 2), "tops": round(2 * M * N * K / us / 1e6, 1), "kernel": lst[0].kernel_name}
+    # int8 dense peak of this GPU, measured here: cuBLASLt int8 8192^3 through torch._int_mm (best of 10)
+    try:
+        y = b8.t()  # [K, N] column-major view
+        torch._int_mm(a8, y)
+        torch.cuda.synchronize()
+        bestt = 1e30
+        for _ in range(10):
+            t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0.record()
+            torch._int_mm(a8, y)
+            t1.record()
+            torch.cuda.synchronize()
+            bestt = min(bestt, t0.elapsed_time(t1))
+        c4["int8_peak_tops"] = round(2 * M * N * K / (bestt * 1e-3) / 1e12, 1)
+        c4["int8_peak_source"] = "torch._int_mm (cuBLASLt int8) 8192^3, best of 10, this run"
+        c4["frac_int8_peak"] = round(c4["tops"] / c4["int8_peak_tops"], 4)
+    except Exception as ex:  # noqa: BLE001
+        c4["int8_peak_tops"] = None
+        c4["int8_peak_source"] = f"unavailable: {type(ex).__name__}: {str(ex)[:120]}"
+    configs["cfg4_i8_i8_multiply_multiply_8192x8192x8192"] = c4
+    del lst
+    torch.cuda.empty_cache()
+    # cfg5: Llama-2-70B FFN 28672 x 8192, W4A16 g128, decode M in {1,16} (HBM-bound) and prefill M = 4096 (tensor-bound)
+    for M in (1, 16):
+        lst = w4_ops(M, 28672, 8192, 4)
+        us = time_graph(torch, lst, 3)
+        configs[f"cfg5_w4a16_M{M}_28672x8192"] = entry(us, M, 28672, 8192, algo_bytes(M, 28672, 8192), lst[0].kernel_name, tensor=False)
+        del lst
+        torch.cuda.empty_cache()
+    configs["cfg5_w4a16_M4096_28672x8192"] = prefill["shapes"]["N28672_K8192"]
+    return prefill, configs
+
+
+def cfg5_sharded(torch, dist, capi, ops, dev, rank, world):
+    """ONE global W4A16 weight N = 28672, K = 8192 (same seed on every rank), column-sharded: rank g owns channels
+    [g N/G, (g+1) N/G) of the packed weight and scales.  Per M: the shard GEMM alone and the shard GEMM followed by the
+    all-gather of the E slices into the pre-allocated E_all[G][M][N/G], both captured in ONE CUDA graph per rank
+    (NCCL all_gather_into_tensor is graph-capturable); max over ranks."""
+    N, K = 28672, 8192
+    n_loc = N // world
+    assert n_loc % 16 == 0
+    lib = capi.lib()
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(777)  # identical global weight on every rank
+    nrot = int(max(2, min(16, 300e6 // (n_loc * K // 2) + 1)))
+    shards = []
+    for _ in range(nrot):
+        packed = torch.randint(0, 256, (int(lib.ckb_prepack_b_int4_bytes(N, K)),), dtype=torch.uint8, device=dev, generator=gen)
+        sc = (torch.rand(K // GROUP, N, device=dev, generator=gen) * 0.015 + 0.005).bfloat16()
+        per_group = (K // 64) * 512  # bytes of one 16-channel group in the fragment-major layout: shards are contiguous
+        g0 = rank * n_loc // 16
+        shards.append((packed[g0 * per_group:(g0 + n_loc // 16) * per_group].clone(), sc[:, rank * n_loc:(rank + 1) * n_loc].contiguous()))
+        del packed, sc
+    torch.cuda.empty_cache()
+    out = {"N": N, "K": K, "world": world, "scaling": "strong", "launch": "cuda-graph replay incl. the NCCL all-gather", "M": {}}
+    st = torch.cuda.Stream(device=dev)
+    for M in (1, 16, 4096):
+        a = torch.randn(M, K, device=dev, generator=gen).bfloat16()
+        e_loc = [torch.empty(M, n_loc, dtype=torch.bfloat16, device=dev) for _ in range(nrot)]
+        e_all = torch.empty(world * M, n_loc, dtype=torch.bfloat16, device=dev)
+        lst = [ops.GemmOp(a, p, e, b_dtype=capi.I4, b_layout=capi.PREPACKED, b_op=capi.BOP_GROUP, N=n_loc, K=K, scale=s,
+                          zero_const=8, group_size=GROUP) for (p, s), e in zip(shards, e_loc)]
+
+        def run(gather):
+            for op, e in zip(lst, e_loc):
+                op.run(st.cuda_stream)
+                if gather:
+                    dist.all_gather_into_tensor(e_all, e)
+        res = {}
+        for gather in (False, True):
+            with torch.cuda.stream(st):
+                run(gather)
+                torch.cuda.synchronize()
+                dist.barrier()
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=st):
+                    run(gather)
+                g.replay()
+                torch.cuda.synchronize()
+                dist.barrier()
+                t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                t0.record(st)
+                for _ in range(3):
+                    g.replay()
+                t1.record(st)
+                torch.cuda.synchronize()
+                dist.barrier()
+            t = torch.tensor([t0.elapsed_time(t1) * 1e3 / (3 * nrot)], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            res["gemm_gather_us" if gather else "gemm_us"] = round(float(t.item()), 2)
+            del g
+        gbytes = 2 * M * N  # bytes every rank holds after the gather
+        res["tflops_gemm"] = round(2 * M * N * K / res["gemm_us"] / 1e6, 2)
+        res["tflops_gemm_gather"] = round(2 * M * N * K / res["gemm_gather_us"] / 1e6, 2)
+        res["gbps_gemm"] = round(algo_bytes(M, N, K) / res["gemm_us"] / 1e3, 1)
+        res["gbps_gemm_gather"] = round(algo_bytes(M, N, K) / res["gemm_gather_us"] / 1e3, 1)
+        res["gather_over_gemm"] = round(res["gemm_us"] / res["gemm_gather_us"], 3)
+        dt_g = max(1e-3, res["gemm_gather_us"] - res["gemm_us"])
+        res["gather_payload_bytes_per_rank"] = gbytes
+        res["gather_gbps_vs_900"] = round(gbytes * (world - 1) / world / dt_g / 1e3, 1)
+        out["M"][str(M)] = res
+        del lst, e_loc, e_all
+    return out
+
 
 
 def cpu_baseline(min_seconds=10.0):

@@ -1,6 +1,11 @@
 // api.cu -- the C ABI of libckb.so (include/ckb.h): argument validation (CK's IsSupportedArgument),
 // kernel selection (CK's instance choice), workspace sizing, launch.  No CPU fallback exists here.
 #include "common.cuh"
+#include <memory>
+#include <mutex>
+#include <unordered_map>
+#include <vector>
+
 #include "kernels.h"
 
 namespace ckb {
@@ -272,6 +277,51 @@ uint64_t ckb_gemm_host_staging_bytes(const ckb_gemm_problem* p)
     return b;
 }
 
+// Plans of the host-buffer entry points, keyed by the bytes of the staged problem.  Entries are never mutated after insertion
+// and live until the cache is reset (when it exceeds its bound), so the returned pointer stays valid for the call.
+namespace {
+struct PlanCache
+{
+    struct Entry { ckb_gemm_problem prob; ckb_gemm_plan plan; };
+    std::mutex mu;
+    std::unordered_multimap<uint64_t, std::unique_ptr<Entry>> map;
+    std::vector<std::unique_ptr<Entry>> retired; // entries of a reset cache stay alive: another thread may still hold one
+};
+PlanCache& plan_cache() { static PlanCache c; return c; }
+thread_local int g_last_rc = CKB_OK;
+int last_error_code() { return g_last_rc; }
+
+const ckb_gemm_plan* cached_plan(const ckb_gemm_problem& q)
+{
+    static const bool enabled = !(getenv("CKB_PLAN_CACHE") && atoi(getenv("CKB_PLAN_CACHE")) == 0);
+    uint64_t h = 1469598103934665603ull; // FNV-1a over the struct bytes
+    const unsigned char* b = reinterpret_cast<const unsigned char*>(&q);
+    for(size_t i = 0; i < sizeof q; ++i) h = (h ^ b[i]) * 1099511628211ull;
+    PlanCache& c = plan_cache();
+    if(enabled)
+    {
+        std::lock_guard<std::mutex> lk(c.mu);
+        auto range = c.map.equal_range(h);
+        for(auto it = range.first; it != range.second; ++it)
+            if(memcmp(&it->second->prob, &q, sizeof q) == 0) return &it->second->plan;
+    }
+    auto e = std::make_unique<PlanCache::Entry>();
+    e->prob = q;
+    if(int rc = ckb_gemm_query(&q, &e->plan)) { g_last_rc = rc; return nullptr; }
+    std::lock_guard<std::mutex> lk(c.mu);
+    if(c.map.size() >= 16384 || c.retired.size() >= 16384)
+    {
+        for(auto& kv : c.map) c.retired.push_back(std::move(kv.second));
+        c.map.clear();
+        if(c.retired.size() >= 65536) c.retired.erase(c.retired.begin(), c.retired.begin() + 32768);
+    }
+    const ckb_gemm_plan* out = &e->plan;
+    if(enabled) c.map.emplace(h, std::move(e));
+    else { c.retired.push_back(std::move(e)); if(c.retired.size() > 1024) c.retired.erase(c.retired.begin(), c.retired.begin() + 512); }
+    return out;
+}
+} // namespace
+
 static int run_host_impl(const ckb_gemm_problem* pp, void* staging, void* workspace, void* stream, bool sync)
 {
     if(!pp || !staging) return set_error(CKB_ERR_INVALID, "null problem/staging");
@@ -303,10 +353,12 @@ static int run_host_impl(const ckb_gemm_problem* pp, void* staging, void* worksp
     // E: the epilogue stores straight into mapped pinned host memory (posted PCIe writes) when it can; otherwise staging + copy
     void* e_alias = mapped_alias(pp->e);
     q.e = e_alias ? e_alias : cur;
-    ckb_gemm_plan plan;
-    if(int rc = ckb_gemm_query(&q, &plan)) return rc;
-    if(!plan.supported) return set_error(CKB_ERR_UNSUPPORTED, "%s", last_error().c_str());
-    if(int rc = ckb_gemm_run(&q, &plan, workspace, stream)) return rc;
+    // the plan (validation + TMA descriptors) depends only on the staged problem: cached per distinct problem, so a serving
+    // loop that re-issues the same GEMMs pays for ckb_gemm_query once (round 1: ~15 us of host time per call went there)
+    const ckb_gemm_plan* plan = cached_plan(q);
+    if(!plan) return last_error_code();
+    if(!plan->supported) return set_error(CKB_ERR_UNSUPPORTED, "%s", last_error().c_str());
+    if(int rc = ckb_gemm_run(&q, plan, workspace, stream)) return rc;
     const uint64_t e_bytes = (uint64_t(pp->M - 1) * pp->lde + pp->N) * dtype_bytes(pp->e_dtype);
     if(!e_alias) CKB_CUDA_CHECK(cudaMemcpyAsync(pp->e, cur, e_bytes, cudaMemcpyDeviceToHost, st));
     if(sync) CKB_CUDA_CHECK(cudaStreamSynchronize(st));

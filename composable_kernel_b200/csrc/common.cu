@@ -24,17 +24,18 @@ int set_error(int code, const char* fmt, ...)
 
 const DeviceInfo& device_info()
 {
-    static DeviceInfo info;
-    static std::once_flag once;
-    std::call_once(once, [] {
-        int n = 0;
-        if(cudaGetDeviceCount(&n) != cudaSuccess || n == 0)
-        {
-            cudaGetLastError();
-            return;
-        }
-        int dev = 0;
-        cudaGetDevice(&dev);
+    static DeviceInfo infos[64];
+    static std::once_flag once[64];
+    static DeviceInfo none;
+    int n = 0, dev = 0;
+    if(cudaGetDeviceCount(&n) != cudaSuccess || n == 0)
+    {
+        cudaGetLastError();
+        return none;
+    }
+    if(cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return none;
+    std::call_once(once[dev], [dev] {
+        DeviceInfo& info = infos[dev];
         cudaDeviceProp p{};
         if(cudaGetDeviceProperties(&p, dev) != cudaSuccess) return;
         info.sm_count = p.multiProcessorCount;
@@ -43,7 +44,7 @@ const DeviceInfo& device_info()
         cudaDeviceGetAttribute(&info.max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
         info.ok = (p.major == 10);
     });
-    return info;
+    return infos[dev];
 }
 
 using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,

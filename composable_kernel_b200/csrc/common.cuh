@@ -4,6 +4,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <cstdarg>
 #include <cstdint>
 #include <cstdio>
@@ -32,7 +33,23 @@ struct DeviceInfo
     int cc_major = 0, cc_minor = 0;
     int max_smem_optin = 0;
 };
-const DeviceInfo& device_info();
+const DeviceInfo& device_info(); // of the CURRENT device (one record per device ordinal)
+
+// Once-per-device guard for cudaFuncSetAttribute: function attributes are per device, so a process-wide flag set on the first
+// device would leave the kernel without its shared-memory opt-in on the others.  Thread-safe; two racing threads may both set the
+// (idempotent) attribute.
+struct PerDeviceOnce
+{
+    std::atomic<uint64_t> done{0};
+    bool need(uint64_t& bit)
+    {
+        int dev = 0;
+        if(cudaGetDevice(&dev) != cudaSuccess) dev = 0;
+        bit = uint64_t(1) << (dev & 63);
+        return !(done.load(std::memory_order_acquire) & bit);
+    }
+    void mark(uint64_t bit) { done.fetch_or(bit, std::memory_order_release); }
+};
 
 // 2-D row-major tensor [rows][cols] with leading dimension ld (elements); box [box_rows][box_cols],
 // 128-byte swizzle (box_cols * elem_bytes must be <= 128 for swizzled boxes; we always use == 128

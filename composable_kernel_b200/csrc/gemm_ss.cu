@@ -442,7 +442,7 @@ gemm_ss2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             }
             ptx::tcgen05_fence_before_sync();
             __syncwarp();
-            if(lane == 0) ptx::mbar_arrive_cluster(ptx::leader_addr(tempty_bar(as)));
+            if(lane == 0) ptx::mbar_arrive_remote(ptx::leader_addr(tempty_bar(as)));
             if(++as == 2) { as = 0; aph ^= 1; }
         }
     }
@@ -520,12 +520,13 @@ int run_gemm_ss(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStream
     a.idesc     = i8 ? ptx::make_idesc(2, 1, 1, SS_BM, SS_BN)
                      : ptx::make_idesc(1, p.a_dtype == CKB_BF16 ? 1 : 0, p.a_dtype == CKB_BF16 ? 1 : 0, SS_BM, SS_BN);
     fill_epi(p, a.ep);
-    static bool attr_set = false;
-    if(!attr_set)
+    static PerDeviceOnce attr_once;
+    uint64_t dev_bit = 0;
+    if(attr_once.need(dev_bit))
     {
         CKB_CUDA_CHECK(cudaFuncSetAttribute(gemm_ss_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SS_SMEM));
         CKB_CUDA_CHECK(cudaFuncSetAttribute(gemm_ss2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SS2_SMEM));
-        attr_set = true;
+        attr_once.mark(dev_bit);
     }
     if(sp->pair)
     {

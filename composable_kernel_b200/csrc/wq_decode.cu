@@ -576,14 +576,15 @@ int launch_decode(const WQPlan* wp, const DQArgs& a, const ckb_gemm_plan& plan, 
 {
     auto kfn = wq_decode_kernel<N_MMA, WF, F16>;
     constexpr int smem = dq_smem_bytes(N_MMA, WF);
-    static bool attr_set = false;
-    if(!attr_set)
+    static PerDeviceOnce attr_once;
+    uint64_t dev_bit = 0;
+    if(attr_once.need(dev_bit))
     {
         CKB_CUDA_CHECK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         // without this the driver sizes the L1/shared carve-out for ONE block and the second CTA never fits
         CKB_CUDA_CHECK(cudaFuncSetAttribute(kfn, cudaFuncAttributePreferredSharedMemoryCarveout,
                                             cudaSharedmemCarveoutMaxShared));
-        attr_set = true;
+        attr_once.mark(dev_bit);
         if(getenv("CK_LOGGING"))
         {
             int nb = 0;

@@ -449,7 +449,7 @@ wq_fused_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             }
             ptx::tcgen05_fence_before_sync();
             __syncwarp();
-            if(lane == 0) ptx::mbar_arrive_cluster(ptx::leader_addr(tempty_bar(as)));
+            if(lane == 0) ptx::mbar_arrive_remote(ptx::leader_addr(tempty_bar(as)));
             if(++as == 2) { as = 0; aph ^= 1; }
         }
         if(args.tma_store && lane == 0) ptx::tma_store_wait<0>();

@@ -446,13 +446,14 @@ template <int NT, int GW, bool F16, bool ZP>
 static int launch_gemv(const GVPlan* gp, const GVArgs& a, int grid, cudaStream_t stream)
 {
     auto kfn = wq_gemv_kernel<NT, GW, F16, ZP>;
-    static bool attr_set = false;
-    if(!attr_set)
+    static PerDeviceOnce attr_once;
+    uint64_t dev_bit = 0;
+    if(attr_once.need(dev_bit))
     {
         CKB_CUDA_CHECK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         // without this the driver sizes the L1/shared carve-out for ONE block and a second CTA never fits
         CKB_CUDA_CHECK(cudaFuncSetAttribute(kfn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-        attr_set = true;
+        attr_once.mark(dev_bit);
     }
     cudaLaunchConfig_t cfg{};
     cfg.gridDim          = dim3(grid);

@@ -130,13 +130,15 @@ class GroupedGemmOp:
         self.supported = rc == 0
         self.why = capi.last_error() if rc else ""
         self._keep = (as_, b0s, b1s, d0s, es)
+        # GroupedGemmMultiABDKernelArgument<1, num_b, num_d> as the C++ compiler lays it out: a zero-length std::array member
+        # still occupies storage (one byte + padding), so NumD = 0 has the offsets of NumD = 1 with the D slots unused
         stride = int(lib.ckb_grouped_gemm_arg_bytes(num_b, num_d))
         blob = bytearray()
         for i in range(G):
             ptrs = [as_[i].data_ptr(), b0s[i].data_ptr()] + ([b1s[i].data_ptr()] if num_b == 2 else []) + \
-                   ([d0s[i].data_ptr()] if num_d else []) + [es[i].data_ptr()]
+                   [d0s[i].data_ptr() if num_d else 0] + [es[i].data_ptr()]
             ints = [as_[i].shape[0], N, K, as_[i].stride(0), b0s[i].stride(0)] + ([0] if num_b == 2 else []) + \
-                   ([d0_stride] if num_d else []) + [es[i].stride(0)]
+                   [d0_stride if num_d else 0] + [es[i].stride(0)]
             rec = struct.pack(f"<{len(ptrs)}Q{len(ints)}i", *ptrs, *ints)
             blob += rec + b"\0" * (stride - len(rec))
         self.dev_args = torch.frombuffer(blob, dtype=torch.uint8).cuda() if G else None
