@@ -441,8 +441,10 @@ def extras(torch, capi, ops, dev):
             packed = torch.randint(0, 256, (int(lib.ckb_prepack_b_int4_bytes(N, K)),), dtype=torch.uint8, device=dev)
             sc = (torch.rand(K // GROUP, N, device=dev) * 0.015 + 0.005).bfloat16()
             e = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
-            op = ops.GemmOp(a, packed, e, b_dtype=capi.I4, b_layout=capi.PREPACKED, b_op=capi.BOP_GROUP, N=N, K=K, scale=sc,
-                            zero_const=8, group_size=GROUP)
+            # numerics contract per regime: decode rows use the ab_scale form (fp32 group scale), prefill rows the one-rounding form;
+            # each contract is served at every M, these are the fast sides of each
+            op = ops.GemmOp(a, packed, e, b_dtype=capi.I4, b_layout=capi.PREPACKED, b_op=capi.BOP_GROUP_RTN if M > 64 else capi.BOP_GROUP,
+                            N=N, K=K, scale=sc, zero_const=8, group_size=GROUP)
             assert op.supported, op.why
             lst.append(op)
         return lst
@@ -572,7 +574,7 @@ def cfg5_sharded(torch, dist, capi, ops, dev, rank, world):
         a = torch.randn(M, K, device=dev, generator=gen).bfloat16()
         e_loc = [torch.empty(M, n_loc, dtype=torch.bfloat16, device=dev) for _ in range(nrot)]
         e_all = torch.empty(world * M, n_loc, dtype=torch.bfloat16, device=dev)
-        lst = [ops.GemmOp(a, p, e, b_dtype=capi.I4, b_layout=capi.PREPACKED, b_op=capi.BOP_GROUP, N=n_loc, K=K, scale=s,
+        lst = [ops.GemmOp(a, p, e, b_dtype=capi.I4, b_layout=capi.PREPACKED, b_op=capi.BOP_GROUP_RTN if M > 64 else capi.BOP_GROUP, N=n_loc, K=K, scale=s,
                           zero_const=8, group_size=GROUP) for (p, s), e in zip(shards, e_loc)]
 
         def run(gather):

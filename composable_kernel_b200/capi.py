@@ -17,7 +17,8 @@ LIB_PATH = os.environ.get("CKB_LIB") or os.path.join(_HERE, "lib", "libckb.so")
 # enums (include/ckb.h)
 F32, F16, BF16, I8, U8, I32, I4 = range(7)
 ROW, COL, PREPACKED = 0, 1, 2
-BOP_PASSTHROUGH, BOP_MULTIPLY, BOP_FPAINTB, BOP_GROUP = range(4)
+BOP_PASSTHROUGH, BOP_MULTIPLY, BOP_FPAINTB, BOP_GROUP, BOP_GROUP_RTN = range(5)
+FLAG_BF16_RNE, FLAG_FIXED_K_ORDER = 1, 2
 (CDE_PASSTHROUGH, CDE_ADD, CDE_FASTGELU, CDE_ADD_FASTGELU, CDE_MULTIPLY, CDE_MULTIPLY_ADD,
  CDE_MULTIPLY_FASTGELU, CDE_MULTIPLY_ADD_FASTGELU, CDE_MULTIPLY_MULTIPLY, CDE_ACT_MUL_CLAMP,
  CDE_ADD_ACT_MUL_CLAMP, CDE_ACT_MUL2_CLAMP, CDE_ADD_ACT_MUL2_CLAMP) = range(13)

@@ -38,7 +38,7 @@ uint64_t algo_bytes(const ckb_gemm_problem& p)
     uint64_t b = uint64_t(p.M) * p.K * dtype_bytes(p.a_dtype);
     if(p.b_dtype == CKB_I4) b += uint64_t(p.N) * p.K / 2;
     else b += uint64_t(p.N) * p.K * dtype_bytes(p.b_dtype);
-    if(p.b_op == CKB_BOP_GROUP && p.group_size > 0)
+    if((p.b_op == CKB_BOP_GROUP || p.b_op == CKB_BOP_GROUP_RTN) && p.group_size > 0)
     {
         const uint64_t g = (p.K + p.group_size - 1) / p.group_size;
         b += g * p.N * dtype_bytes(p.s_dtype);
@@ -150,6 +150,7 @@ int ckb_gemm_query(const ckb_gemm_problem* pp, ckb_gemm_plan* plan)
     switch(p.b_op)
     {
     case CKB_BOP_GROUP:
+    case CKB_BOP_GROUP_RTN:
         if(p.b_dtype != CKB_I4 || p.b_layout != CKB_PREPACKED) return unsupported(plan, "GROUP dequant needs pre-packed int4 B (ckb_prepack_b_int4)");
         if(p.group_size != 128) return unsupported(plan, "group_size must be 128");
         if(!p.scale || p.s_dtype != p.a_dtype) return unsupported(plan, "group scales must have A's type");
@@ -170,7 +171,8 @@ int ckb_gemm_query(const ckb_gemm_problem* pp, ckb_gemm_plan* plan)
         break;
     default: return unsupported(plan, "unknown b_op %d", p.b_op);
     }
-    if(p.b_op != CKB_BOP_GROUP)
+    const bool w4 = p.b_op == CKB_BOP_GROUP || p.b_op == CKB_BOP_GROUP_RTN;
+    if(!w4)
     {
         if(p.b_layout != CKB_COL) return unsupported(plan, "int8 B must be K-major (column-major: mk_nk_mn)");
         if(p.ldb % 16 || p.ldb < p.K) return unsupported(plan, "ldb must be a multiple of 16 and >= K");
@@ -178,7 +180,11 @@ int ckb_gemm_query(const ckb_gemm_problem* pp, ckb_gemm_plan* plan)
     if(p.lda % 8 || p.lda < p.K) return unsupported(plan, "lda must be a multiple of 8 and >= K");
     if(p.lde < p.N) return unsupported(plan, "lde < N");
     if(!device_info().ok) { plan->supported = 0; return set_error(CKB_ERR_NO_DEVICE, "no sm_100 device"); }
-    if(p.M > 64 && p.K % 8 == 0)
+    // The two W4A16 numerics contracts keep their definition at EVERY M (no switch at the decode / prefill boundary):
+    // GROUP (fp32 group scale on partial sums) is always served by the HMMA decode kernels, in row slabs above 64 rows;
+    // GROUP_RTN (one rounding into A's type) by the fused tcgen05 kernel above 64 rows and by the RTN instantiation of the
+    // HMMA kernel below.
+    if(p.M > 64 && p.K % 8 == 0 && p.b_op != CKB_BOP_GROUP)
     {
         // prefill-shaped: the fused TMA -> dequant -> tcgen05 pair kernel (no workspace).  CKB_PREFILL_TWO_PASS=1 selects the
         // round-1 form (expand the weight into the workspace, then the dense GEMM) for comparison.
@@ -188,23 +194,27 @@ int ckb_gemm_query(const ckb_gemm_problem* pp, ckb_gemm_plan* plan)
         plan->supported = 1;
         return CKB_OK;
     }
-    if(p.b_op == CKB_BOP_GROUP)
+    if(w4)
     {
         // W4A16, M <= 64 (larger M with K % 8 != 0: slabs): N-split HMMA kernels, no workspace.  Two schedules of the same
         // math (profiles/r2_gemv_variants.txt): the rotating-producer kernel (wq_gemv2, <= 32 rows per launch) wins where one
         // pass covers the CTA's channels and either M <= 8 or the whole K extent is resident in the ring; the single-producer
         // kernel (wq_gemv, <= 64 rows) wins on streaming shapes and on M > 8.  CKB_GEMV=1 / 2 forces one of them.
         const int force = getenv("CKB_GEMV") ? atoi(getenv("CKB_GEMV")) : 0;
-        bool old_kernel = force == 1 || p.M > 32;
-        if(!old_kernel && force != 2)
+        // RTN numerics and the fixed-K-order contract exist in the rotating-producer kernel only
+        const bool g2_only = p.b_op == CKB_BOP_GROUP_RTN || (p.flags & CKB_FLAG_FIXED_K_ORDER);
+        // rows beyond 32 go through 32-row slabs: the single-producer kernel's 64-row variant (8 token tiles) is retired -- its
+        // activation stage overflows the ring on K >= 4096 (mbarrier time-out found by tests/slab_probe.py)
+        bool old_kernel = !g2_only && force == 1;
+        if(!old_kernel && force != 2 && !g2_only)
         {
             G2Sched s{};
             const int sms = device_info().sm_count > 0 ? device_info().sm_count : 148;
-            if(schedule_wq_gemv2(p.M, p.N, p.K, p.zero != nullptr, sms, s) != CKB_OK) old_kernel = true;
+            if(schedule_wq_gemv2(std::min(p.M, 32), p.N, p.K, p.zero != nullptr, sms, s) != CKB_OK) old_kernel = true;
             else old_kernel = !(s.passes == 1 && (s.nt == 1 || s.ring >= s.n_chunks));
         }
         ckb_gemm_problem q = p;
-        q.M = std::min(p.M, old_kernel ? 64 : 32);
+        q.M = std::min(p.M, 32);
         if(int rc = old_kernel ? plan_wq_gemv(q, *plan) : plan_wq_gemv2(q, *plan)) { if(rc == CKB_ERR_UNSUPPORTED) { plan->supported = 0; return CKB_OK; } return rc; }
         plan->kernel_id = old_kernel ? KID_WQ_GEMV : KID_WQ_GEMV2;
         plan->supported = 1;
@@ -237,7 +247,7 @@ int ckb_gemm_run(const ckb_gemm_problem* pp, const ckb_gemm_plan* plan, void* wo
     case KID_WQ_GEMV2:
     case KID_WQ_DECODE: {
         const int kid  = plan->kernel_id;
-        const int slab = kid == KID_WQ_GEMV2 ? 32 : 64; // rows one launch of the kernel handles
+        const int slab = kid == KID_WQ_DECODE ? 64 : 32; // rows one launch of the kernel handles
         auto plan_one = [&](const ckb_gemm_problem& q, ckb_gemm_plan& pl) {
             return kid == KID_WQ_GEMV2 ? plan_wq_gemv2(q, pl) : (kid == KID_WQ_GEMV ? plan_wq_gemv(q, pl) : plan_wq_decode(q, pl));
         };

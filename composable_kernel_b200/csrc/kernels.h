@@ -52,7 +52,9 @@ struct G2Sched
     int nt, rb, n_groups, kb_total, grid, passes, n_slots, slot_q, slot_r, g_hi, wn_log2, gw, kbu, upw, n_chunks, ring;
     int stage_bytes, off_w, off_s, off_z, red_off, bar_off, smem_bytes;
 };
-int schedule_wq_gemv2(int M, int N, int K, bool zp, int sms, G2Sched& s);
+// mode bits: 1 = fixed K order (CKB_FLAG_FIXED_K_ORDER: 2 x 8 / 1 x 8 warps, one 128-k unit per warp and stage, whatever N is),
+//            2 = RTN numerics (CKB_BOP_GROUP_RTN: scale applied per weight, 128-k units only)
+int schedule_wq_gemv2(int M, int N, int K, bool zp, int sms, G2Sched& s, int mode = 0);
 int plan_wq_gemv2(const ckb_gemm_problem& p, ckb_gemm_plan& plan);
 int run_wq_gemv2(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStream_t stream);
 int plan_wq_prefill(const ckb_gemm_problem& p, ckb_gemm_plan& plan);

@@ -119,7 +119,7 @@ int plan_wq_prefill(const ckb_gemm_problem& p, ckb_gemm_plan& plan)
     plan.block          = 256;
     plan.split_units    = 1;
     static const char* wfn[] = {"w4g128", "w8mul", "w8fpaintb", "w8pass"};
-    const int wf = p.b_op == CKB_BOP_GROUP ? 0 : (p.b_op == CKB_BOP_MULTIPLY ? 1 : (p.b_op == CKB_BOP_FPAINTB ? 2 : 3));
+    const int wf = p.b_op == CKB_BOP_GROUP_RTN ? 0 : (p.b_op == CKB_BOP_MULTIPLY ? 1 : (p.b_op == CKB_BOP_FPAINTB ? 2 : 3));
     snprintf(plan.kernel_name, sizeof plan.kernel_name, "wq_prefill_%s_%s_dequant+gemm_ss_tcgen05_128x256x64", wfn[wf],
              p.a_dtype == CKB_F16 ? "f16" : "bf16");
     return CKB_OK;
@@ -132,7 +132,7 @@ int run_wq_prefill(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, void* w
     uint16_t* bdq    = static_cast<uint16_t*>(workspace);
     const bool f16   = p.a_dtype == CKB_F16;
     const int blocks = 148 * 8;
-    if(p.b_op == CKB_BOP_GROUP)
+    if(p.b_op == CKB_BOP_GROUP_RTN)
     {
         const int n_groups = (p.N + 15) / 16, k_tiles = (p.K + 63) / 64;
         const long long chunks = (long long)n_groups * k_tiles * 32;

@@ -472,7 +472,7 @@ struct FUPlan
 
 int weight_format(const ckb_gemm_problem& p)
 {
-    return p.b_op == CKB_BOP_GROUP ? WF_W4_GROUP : (p.b_op == CKB_BOP_MULTIPLY ? WF_W8_MUL : (p.b_op == CKB_BOP_FPAINTB ? WF_W8_FPAINTB : WF_W8_PASS));
+    return p.b_op == CKB_BOP_GROUP_RTN ? WF_W4_GROUP : (p.b_op == CKB_BOP_MULTIPLY ? WF_W8_MUL : (p.b_op == CKB_BOP_FPAINTB ? WF_W8_FPAINTB : WF_W8_PASS));
 }
 
 template <int WF, bool F16>

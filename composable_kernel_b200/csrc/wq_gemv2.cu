@@ -31,8 +31,9 @@ int launch_gemv2_variant(bool f16, int nt, int gw, int kbu, const G2Plan* gp, co
 
 // Host-side schedule of the decode kernel (also exercised without a GPU by tests/test_capi_cpu.py through
 // ckb_gemv_schedule): how the n16 channel groups and the K range are cut into (CTA, pass, stage, warp) work.
-int schedule_wq_gemv2(int M, int N, int K, bool zp, int sms, G2Sched& s)
+int schedule_wq_gemv2(int M, int N, int K, bool zp, int sms, G2Sched& s, int mode)
 {
+    const bool fixed = mode & 1, rtn = mode & 2;
     if(M < 1 || M > 32) return set_error(CKB_ERR_UNSUPPORTED, "W4 decode kernel handles 1 <= M <= 32 per launch");
     s.nt = M <= 8 ? 1 : (M <= 16 ? 2 : 4);
     s.rb = s.nt == 1 ? (M <= 1 ? 1 : (M <= 2 ? 2 : (M <= 4 ? 4 : 8))) : 8 * s.nt;
@@ -43,7 +44,7 @@ int schedule_wq_gemv2(int M, int N, int K, bool zp, int sms, G2Sched& s)
     s.grid     = std::max(1, std::min(sms, s.n_groups));
     s.grid     = std::max(1, std::min(env_int("CKB_GEMV_GRID", s.grid), s.n_groups));
     // groups per slot: up to 2 x GW with the warps split into two channel halves (M <= 8), GW otherwise
-    const int gmax    = std::max(1, std::min((s.nt == 1 ? 2 : 1) * gwmx, env_int("CKB_G2_GMAX", 99)));
+    const int gmax    = std::max(1, std::min((s.nt == 1 ? 2 : 1) * gwmx, fixed ? 99 : env_int("CKB_G2_GMAX", 99)));
     const int per_cta = (s.n_groups + s.grid - 1) / s.grid;
     s.passes  = (per_cta + gmax - 1) / gmax;
     s.n_slots = s.grid * s.passes;
@@ -52,10 +53,15 @@ int schedule_wq_gemv2(int M, int N, int K, bool zp, int sms, G2Sched& s)
     s.g_hi    = s.slot_q + (s.slot_r ? 1 : 0);
     // 16 warps: all on K (1 x 16) while a warp can hold the slot's groups in <= 64 registers (<= 2), else 2 x 8
     s.wn_log2 = (s.nt == 1 && s.g_hi > 2) ? 1 : 0;
-    if(s.nt == 1) s.wn_log2 = std::max(0, std::min(1, env_int("CKB_G2_WN", s.wn_log2 + 1) - 1));
+    if(s.nt == 1 && !fixed) s.wn_log2 = std::max(0, std::min(1, env_int("CKB_G2_WN", s.wn_log2 + 1) - 1));
+    // fixed K order: the warp grid and the K units of a stage must not depend on N or on the grid (see CKB_FLAG_FIXED_K_ORDER)
+    if(fixed) s.wn_log2 = s.nt == 1 ? 1 : 0;
     if((s.g_hi + (1 << s.wn_log2) - 1 >> s.wn_log2) > gwmx) s.wn_log2 = 1;
     const int wn = 1 << s.wn_log2, wk = nw / wn;
     s.gw      = (s.g_hi + wn - 1) / wn;
+    // fixed K order: a warp with one group runs two interleaved accumulation chains (NCH = 2), which is a different fp32
+    // order -- keep at least two group slots per warp (the second one may stay empty)
+    if(fixed) s.gw = std::max(s.gw, 2);
     const int g_alloc = wn * s.gw; // groups a stage has room for (a warp with gw - 1 groups reads one dead group)
     auto al = [](int v, int a) { return (v + a - 1) / a * a; };
     const int red_bytes = nw * s.gw * s.nt * 512;
@@ -69,8 +75,13 @@ int schedule_wq_gemv2(int M, int N, int K, bool zp, int sms, G2Sched& s)
     for(int kbu : {2, 1})
         for(int upw : {4, 2, 1})
         {
-            if(int e = env_int("CKB_G2_KBU", 0)) { if(e != kbu) continue; }
-            if(int e = env_int("CKB_G2_UPW", 0)) { if(e != upw) continue; }
+            if(fixed) { if(kbu != 2 || upw != 1) continue; }
+            else
+            {
+                if(int e = env_int("CKB_G2_KBU", 0)) { if(e != kbu) continue; }
+                if(int e = env_int("CKB_G2_UPW", 0)) { if(e != upw) continue; }
+            }
+            if(rtn && kbu != 2) continue;
             if(kbu == 1 && upw > 1 && s.rb == 4) continue; // the swizzle phase of the activation rows would depend on the unit
             const int chk    = wk * upw * kbu, rows = chk / 2;
             if(chk > 256 || (upw > 1 && wk * (upw / 2) * kbu >= s.kb_total)) continue; // TMA box limit; no point in empty units
@@ -117,11 +128,13 @@ int plan_wq_gemv2(const ckb_gemm_problem& p, ckb_gemm_plan& plan)
     const bool zp  = p.zero != nullptr;
     const int sms  = device_info().sm_count > 0 ? device_info().sm_count : 148;
     G2Sched s{};
-    if(int rc = schedule_wq_gemv2(p.M, p.N, p.K, zp, sms, s)) return rc;
+    const int mode = ((p.flags & CKB_FLAG_FIXED_K_ORDER) ? 1 : 0) | (p.b_op == CKB_BOP_GROUP_RTN ? 2 : 0);
+    if(int rc = schedule_wq_gemv2(p.M, p.N, p.K, zp, sms, s, mode)) return rc;
     gp->nt = s.nt; gp->gw = s.gw; gp->passes = s.passes; gp->slot_q = s.slot_q; gp->slot_r = s.slot_r; gp->g_hi = s.g_hi;
     gp->wn_log2 = s.wn_log2; gp->kbu = s.kbu; gp->upw = s.upw; gp->n_chunks = s.n_chunks; gp->ring = s.ring; gp->stage_bytes = s.stage_bytes;
     gp->off_w = s.off_w; gp->off_s = s.off_s; gp->off_z = s.off_z;
     gp->red_off = s.red_off; gp->bar_off = s.bar_off; gp->smem_bytes = s.smem_bytes; gp->rb = s.rb;
+    gp->rtn = (mode & 2) ? 1 : 0;
 
     const int chk = (g2_warps(s.nt) >> s.wn_log2) * s.upw * s.kbu;
     const CUtensorMapDataType adt = f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
@@ -163,8 +176,9 @@ int plan_wq_gemv2(const ckb_gemm_problem& p, ckb_gemm_plan& plan)
     plan.smem_bytes      = gp->smem_bytes;
     plan.split_units     = 1;
     plan.workspace_bytes = 0;
-    snprintf(plan.kernel_name, sizeof plan.kernel_name, "wq_gemv2_w4g128_%s_hmma_%dx%dwarps_g%d_p%d_m%d_u%dx%d_r%d", f16 ? "f16" : "bf16",
-             1 << s.wn_log2, g2_warps(s.nt) >> s.wn_log2, s.gw, s.passes, 8 * s.nt, s.upw, s.kbu, s.ring);
+    snprintf(plan.kernel_name, sizeof plan.kernel_name, "wq_gemv2_w4g128%s_%s_hmma_%dx%dwarps_g%d_p%d_m%d_u%dx%d_r%d%s", (mode & 2) ? "rtn" : "",
+             f16 ? "f16" : "bf16", 1 << s.wn_log2, g2_warps(s.nt) >> s.wn_log2, s.gw, s.passes, 8 * s.nt, s.upw, s.kbu, s.ring,
+             (mode & 1) ? "_korder" : "");
     return CKB_OK;
 }
 
@@ -189,6 +203,7 @@ int run_wq_gemv2(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStrea
     a.rb         = gp->rb;
     a.zero_const = p.zero_const;
     a.has_zero   = p.zero != nullptr;
+    a.rtn        = gp->rtn;
     {
         // programmatic dependent launch pays inside a CUDA graph (PDL edges: the next kernel's prologue and weight prefill
         // overlap this one) but an EAGER launch with the attribute costs ~20 us of host time against ~6 us without

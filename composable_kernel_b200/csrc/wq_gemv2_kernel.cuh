@@ -54,6 +54,7 @@ struct G2Args
     int zero_const;
     int has_zero;
     int pdl;        // launch with programmatic stream serialization
+    int rtn;        // CKB_BOP_GROUP_RTN: (q - zp) * s rounded once into A's type before the MMA (RTN kernel instantiation)
     int dbg;        // debug knobs (CKB_GEMV_DBG): 1 = skip the math, 8 = skip the copies and waits
     long long* trace; // trace build: [cta][warp][10] = globaltimer at entry / prefill issued / PDL wait done / first stage full /
                       // K loop done / exit, then clock cycles waiting on full barriers / issuing refills / in the K loop / total
@@ -84,7 +85,7 @@ static __device__ __noinline__ void g2_store_one(const EpiParams& ep, int m, int
 #define G2_TV(k, v) do { } while(0)
 #endif
 
-template <int NT, int GW, int KBU, bool F16, bool ZP>
+template <int NT, int GW, int KBU, bool F16, bool ZP, bool RTN>
 __global__ void __launch_bounds__(g2_threads(NT), 2)
 wq_gemv2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW0,
                 const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ CUtensorMap tmS0,
@@ -93,7 +94,7 @@ wq_gemv2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 {
     constexpr uint32_t MAGIC16 = F16 ? 0x6400u : 0x4300u;
     constexpr int NW  = g2_warps(NT);
-    constexpr int NCH = GW == 1 && NT == 1 ? 2 : 1; // independent HMMA accumulation chains per group
+    constexpr int NCH = GW == 1 && NT == 1 && !RTN ? 2 : 1; // independent HMMA accumulation chains per group
     // M <= 8: the zero point is folded out of the unpack (magic + q goes to the tensor core, 7 instead of 11 instructions per
     // 8 weights: the SM is issue-bound) and (magic + zp) * sum_k a_k is removed from the fp32 partial sums afterwards
     constexpr bool FOLD = false; // zero-point folding (magic + q into the MMA, correction by an extra ones-MMA): measured slower, profiles/r2_gemv_variants.txt
@@ -280,6 +281,9 @@ wq_gemv2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                     const float s_lo = F16 ? __half2float(__ushort_as_half((unsigned short)sl)) : __uint_as_float(sl << 16);
                     const float s_hi = F16 ? __half2float(__ushort_as_half((unsigned short)sh)) : __uint_as_float(sh << 16);
                     if(!FOLD) { zm_lo *= 0x10001u; zm_hi *= 0x10001u; }
+                    // RTN: the weight the MMA sees is (q - zp) * s rounded ONCE (nearest-even) into A's type, the operand a 16-bit
+                    // dequantizing GEMM streams (same definition as the fused prefill kernel); products go straight into acc
+                    const uint32_t sl2 = sl * 0x10001u, sh2 = sh * 0x10001u;
                     // FOLD: magic + q, else exact (q - zp), in A's type -> fp32 partial sums of this unit (inside one scale group)
                     float part[NCH][NT][4];
 #pragma unroll
@@ -296,17 +300,19 @@ wq_gemv2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                         {
                             uint32_t a[4];
                             if(FOLD) dequant_w4_word_magic<F16>(w4[ks], a);
+                            else if(RTN) dequant_w4_word_scaled2<F16>(w4[ks], zm_lo, zm_hi, sl2, sh2, a);
                             else dequant_w4_word_exact2<F16>(w4[ks], zm_lo, zm_hi, a);
 #pragma unroll
                             for(int nt = 0; nt < NT; ++nt)
                             {
                                 const uint4 bb = bf[b][nt][ks >> 1];
-                                float* pp      = part[NCH == 2 ? (ks & 1) : 0][nt];
+                                float* pp      = RTN ? acc[gi][nt] : part[NCH == 2 ? (ks & 1) : 0][nt];
                                 if(ks & 1) ptx::mma_m16n8k16<F16>(pp, a, bb.z, bb.w);
                                 else ptx::mma_m16n8k16<F16>(pp, a, bb.x, bb.y);
                             }
                         }
                     }
+                    if(!RTN)
 #pragma unroll
                     for(int nt = 0; nt < NT; ++nt)
                     {
@@ -403,16 +409,16 @@ struct G2Plan
 {
     CUtensorMap tmA, tmW[2], tmS[2], tmZ[2];
     int32_t nt, gw, passes, slot_q, slot_r, g_hi, wn_log2, kbu, upw, n_chunks, ring, stage_bytes, off_w, off_s, off_z, red_off, bar_off,
-        smem_bytes, rb;
+        smem_bytes, rb, rtn;
 };
 
 // per-(dtype, NT) launchers: each lives in its own translation unit (wq_gemv2_inst.cu, -DGV_INST_F16 / -DGV_INST_NT)
 int launch_gemv2_variant(bool f16, int nt, int gw, int kbu, const G2Plan* gp, const G2Args& a, int grid, cudaStream_t stream);
 
-template <int NT, int GW, int KBU, bool F16, bool ZP>
+template <int NT, int GW, int KBU, bool F16, bool ZP, bool RTN>
 static int launch_gemv2(const G2Plan* gp, const G2Args& a, int grid, cudaStream_t stream)
 {
-    auto kfn = wq_gemv2_kernel<NT, GW, KBU, F16, ZP>;
+    auto kfn = wq_gemv2_kernel<NT, GW, KBU, F16, ZP, RTN>;
     // the opt-in is per device (cudaFuncSetAttribute applies to the current device only): one flag per device ordinal
     static unsigned long long attr_mask = 0;
     int dev = 0;

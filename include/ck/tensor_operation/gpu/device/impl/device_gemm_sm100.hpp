@@ -238,7 +238,7 @@ struct DeviceGemm_dequantB_GroupScale_Sm100
         p.M = M; p.N = N; p.K = K;
         p.a_dtype = ckb_detail::dtype_of<ADataType>(); p.a_layout = ckb_detail::layout_of<ALayout>(); p.a = p_a; p.lda = StrideA;
         p.b_dtype = CKB_I4; p.b_layout = CKB_PREPACKED; p.b = p_b_prepacked;
-        p.b_op = CKB_BOP_GROUP; p.s_dtype = p.a_dtype; p.scale = p_scale; p.zero = p_zero;
+        p.b_op = BElementwiseOperation::kCkbBOp; p.s_dtype = p.a_dtype; p.scale = p_scale; p.zero = p_zero;
         p.zero_const = ZeroPointDefault; p.group_size = GroupSize;
         p.cde_op = CElementwiseOperation::kCkbCde;
         p.e_dtype = ckb_detail::dtype_of<CDataType>(); p.e = p_c; p.lde = StrideC;

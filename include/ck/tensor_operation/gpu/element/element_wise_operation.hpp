@@ -223,11 +223,26 @@ struct Add_Activation_Mul2_Clamp
     Activation activationOp_;
 };
 
-// [EXT] B functor of the W4A16 path: (q - zero[k/G,n]) * scale[k/G,n], rounded once (nearest-even) into A's type.
-// Nearest reference pattern: DeviceGemmMultipleD_ABScale's ScaleBlockK (device/device_gemm_multiple_d_ab_scale.hpp:22-59).
+// [EXT] B functors of the W4A16 path.  Two numerics contracts, each valid at every M (the device op never switches between
+// them by problem size):
+//  * DequantizeGroup -- ab_scale pattern (device/device_gemm_multiple_d_ab_scale.hpp:22-59; host loop
+//    example/65_gemm_multiply_multiply/gemm_multiply_multiply_xdl_fp8_ab_scale.cpp:258-290): the operand is the exact
+//    (q - zero[k/G,n]); scale[k/G,n] multiplies in float.  The functor returns float.
+//  * DequantizeGroupRound -- dequant-in-B-copy pattern (threadwise_tensor_slice_transfer_v3r1_dequant.hpp:509-547): the
+//    operand is (q - zero) * scale rounded once (nearest-even) into A's type.
 struct DequantizeGroup
 {
     static constexpr int kCkbBOp = CKB_BOP_GROUP;
+    void operator()(float& y, const int& q_minus_zero, const float& scale) const { y = float(q_minus_zero) * scale; }
+    template <typename Y>
+    void operator()(float& y, const int& q_minus_zero, const Y& scale) const
+    {
+        y = float(q_minus_zero) * detail::to_f32(scale);
+    }
+};
+struct DequantizeGroupRound
+{
+    static constexpr int kCkbBOp = CKB_BOP_GROUP_RTN;
     template <typename Y>
     void operator()(Y& y, const int& q_minus_zero, const Y& scale) const
     {

@@ -68,7 +68,13 @@ typedef enum ckb_b_op {
     CKB_BOP_PASSTHROUGH = 0, /* PassThrough<AType,int8>                 unary_element_wise_operation.hpp:112-121 */
     CKB_BOP_MULTIPLY    = 1, /* Multiply<bhalf_t,int8_t,bhalf_t>(B0,B1)  binary_element_wise_operation.hpp:184-190 */
     CKB_BOP_FPAINTB     = 2, /* fp16(u8 - 128) * scale[n]                reference_fpAintB_gemm.hpp:110, B = biased uint8 */
-    CKB_BOP_GROUP       = 3  /* [EXT] (q - zp[k/g,n]) * s[k/g,n], fp32   pattern: device_gemm_multiple_d_ab_scale.hpp:22-59 */
+    CKB_BOP_GROUP       = 3, /* [EXT] W4A16 group scale, ab_scale numerics: exact (q - zp[k/g,n]) in A's type into the MMA, the group
+                                scale s[k/g,n] multiplies the fp32 partial sum of each group (host pattern:
+                                gemm_multiply_multiply_xdl_fp8_ab_scale.cpp:258-290; device_gemm_multiple_d_ab_scale.hpp:22-59).
+                                Every M: HMMA decode kernels up to 64 rows per launch, row slabs of them above. */
+    CKB_BOP_GROUP_RTN   = 4  /* [EXT] W4A16 group scale, dequant-in-B-copy numerics: (q - zp) * s rounded ONCE (nearest-even) into
+                                A's type, then a plain 16-bit GEMM (the weight threadwise_tensor_slice_transfer_v3r1_dequant.hpp
+                                :509-547 hands the block GEMM).  Every M: fused tcgen05 kernel above 64 rows, HMMA kernel below. */
 } ckb_b_op;
 
 /* CDE element-wise op (epilogue).  Same numbering as the oracle's orc_cde_op. */
@@ -91,8 +97,12 @@ typedef enum ckb_cde_op {
 typedef enum ckb_act { CKB_ACT_PASSTHROUGH = 0, CKB_ACT_RELU = 1 } ckb_act;
 
 enum {
-    CKB_FLAG_BF16_RNE = 1 << 0 /* round bf16 outputs to nearest-even instead of CK's truncation
+    CKB_FLAG_BF16_RNE = 1 << 0, /* round bf16 outputs to nearest-even instead of CK's truncation
                                   (type_convert.hpp:53-64 vs :508-549); default = truncation */
+    CKB_FLAG_FIXED_K_ORDER = 1 << 1 /* [EXT] W4A16 decode (M <= 64): make the fp32 summation order over K independent of N, of the
+                                  grid and of the shard a problem is cut into, so that G column shards + all-gather reproduce
+                                  the single-GPU E bit for bit.  Without it the planner picks the fastest warp
+                                  grid per shape and two different N may differ in the last bit of a few outputs. */
 };
 
 #define CKB_MAX_D 2

@@ -16,7 +16,7 @@ def from_dev_bf16(t):
     return t.view(torch.int16).cpu().numpy().view(np.uint16)
 
 
-def run_w4a16(a, q_kn, s, z=None, zero_const=8, f16=False, out_f32=False, ds=(), d_strides=(), cde_op=0):
+def run_w4a16(a, q_kn, s, z=None, zero_const=8, f16=False, out_f32=False, ds=(), d_strides=(), cde_op=0, rtn=False, flags=0):
     """a [M,K] (uint16 bf16 bits or float16), q_kn uint8 [K,N] codes, s [K/128,N], z uint8 [K/128,N] or None."""
     import torch
     from composable_kernel_b200 import capi, ops
@@ -26,8 +26,9 @@ def run_w4a16(a, q_kn, s, z=None, zero_const=8, f16=False, out_f32=False, ds=(),
     packed = ops.prepack_int4(to_dev(q_kn))
     zd = to_dev(z) if z is not None else None
     e = torch.zeros(M, N, dtype=torch.float32 if out_f32 else (torch.float16 if f16 else torch.bfloat16), device="cuda")
-    op = ops.GemmOp(ad, packed, e, b_dtype=capi.I4, b_layout=capi.PREPACKED, b_op=capi.BOP_GROUP, N=N, K=K,
-                    scale=sd, zero=zd, zero_const=zero_const, group_size=128, ds=ds, d_strides=d_strides, cde_op=cde_op)
+    # rtn selects the numerics contract (capi.BOP_GROUP_RTN: one rounding into A's type; default capi.BOP_GROUP: fp32 group scale)
+    op = ops.GemmOp(ad, packed, e, b_dtype=capi.I4, b_layout=capi.PREPACKED, b_op=capi.BOP_GROUP_RTN if rtn else capi.BOP_GROUP, N=N, K=K,
+                    scale=sd, zero=zd, zero_const=zero_const, group_size=128, ds=ds, d_strides=d_strides, cde_op=cde_op, flags=flags)
     assert op.supported, op.why
     op.run()
     op.run()  # second run: the self-cleaning stream-K workspace must have been restored

@@ -66,16 +66,25 @@ def case_i8(M, N, K):
     print(f"i8 mulmul M{M} N{N} K{K}: {us:.1f} us  {2*M*N*K/us/1e6:.1f} TOP/s  kernel={lst[0].kernel_name}")
 
 
+def BOP_W4(M):
+    """numerics contract of the W4A16 runs: PERF_RTN=0/1 forces one, default = the fast one of the regime"""
+    r = os.environ.get("PERF_RTN")
+    rtn = (M > 64) if r is None else bool(int(r))
+    return capi.BOP_GROUP_RTN if rtn else capi.BOP_GROUP
+
+
 def case_w4(M, N, K):
     nrot = int(400e6 // (N * K // 2)) + 1
+    nrot = int(os.environ.get("PERF_NROT", nrot))   # small values keep the weights L2-resident (an upper bound for prefetching)
     lst = []
     a = torch.randn(M, K, device="cuda").bfloat16()
     for _ in range(nrot):
         packed = torch.randint(0, 256, (int(capi.lib().ckb_prepack_b_int4_bytes(N, K)),), dtype=torch.uint8, device="cuda")
         sc = (torch.rand(K // 128, N, device="cuda") * 0.01).bfloat16()
         e = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
-        lst.append(ops.GemmOp(a, packed, e, b_dtype=capi.I4, b_layout=capi.PREPACKED, b_op=capi.BOP_GROUP, N=N, K=K,
+        lst.append(ops.GemmOp(a, packed, e, b_dtype=capi.I4, b_layout=capi.PREPACKED, b_op=BOP_W4(M), N=N, K=K,
                               scale=sc, zero_const=8, group_size=128))
+    lst = lst * int(os.environ.get("PERF_REPEAT", 1))   # longer graphs for small rotations
     us = timeit(lst, 5)
     by = 2 * M * K + N * K // 2 + (K // 128) * N * 2 + 2 * M * N
     print(f"w4 M{M} N{N} K{K}: {us:.2f} us  {by/us/1e3:.0f} GB/s  {2*M*N*K/us/1e6:.2f} TFLOP/s  grid={lst[0].plan.grid} kernel={lst[0].kernel_name}")

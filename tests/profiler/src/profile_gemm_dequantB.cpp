@@ -108,37 +108,46 @@ int profile_gemm_w4a16(int argc, char* argv[])
         std::cerr << "prepack failed: " << ckb_last_error() << std::endl;
         return 1;
     }
-    if(do_verification)
-    {
-        Tensor<BF16> b({k, n});
-        for(int i = 0; i < K; ++i) for(int j = 0; j < N; ++j) DequantizeGroup{}(b(i, j), int(q(i, j)) - int(use_zp ? z(i / G, j) : 8), s(i / G, j));
-        Tensor<F32> c({m, n});
-        using Ref = ck::tensor_operation::host::ReferenceGemm<BF16, BF16, F32, F32, PassThrough, PassThrough, PassThrough>;
-        auto ref = Ref{}; auto inv = ref.MakeInvoker(); auto arg = ref.MakeArgument(a, b, c, PassThrough{}, PassThrough{}, PassThrough{});
-        inv.Run(arg);
-        for(int i = 0; i < M; ++i) for(int j = 0; j < N; ++j) PassThrough{}(e_host(i, j), c(i, j));
-    }
-    using Op = ck::tensor_operation::device::DeviceGemm_dequantB_GroupScale_Sm100<Row, Row, BF16, BF16, G, PassThrough, DequantizeGroup, PassThrough>;
-    std::vector<std::unique_ptr<Op>> op_ptrs;
-    op_ptrs.push_back(std::make_unique<Op>());
-    const double bytes = 2.0 * M * K + 0.5 * N * K + 2.0 * kg * N + (use_zp ? 1.0 * kg * N : 0.0) + 2.0 * M * N;
-    const bool pass = ck::profiler::run_instances(
-        op_ptrs,
-        [&](auto& op) {
-            return op.MakeArgumentPointer(a_buf.GetDeviceBuffer(), packed.GetDeviceBuffer(), s_buf.GetDeviceBuffer(), use_zp ? z_buf.GetDeviceBuffer() : nullptr,
-                                          e_buf.GetDeviceBuffer(), M, N, K, K, N, 8, PassThrough{}, DequantizeGroup{}, PassThrough{});
-        },
-        [&](auto& op, auto* arg) {
-            auto ws = std::make_shared<DeviceMem>(op.GetWorkSpaceSize(arg));
-            op.SetWorkSpacePointer(arg, ws->GetDeviceBuffer());
-            return ws;
-        },
-        [&]() {
-            e_buf.FromDevice(e_dev.mData.data());
-            if(do_log) LogRangeAsType<float>(std::cout << "e_device: ", e_dev.mData, ",") << std::endl;
-            return ck::utils::check_err(e_dev, e_host, "Error: Incorrect results!", 1e-2, 1e-2);
-        },
-        do_verification, time_kernel, n_warmup, n_iter, 2.0 * M * N * K, bytes, 1.0);
+    // both numerics contracts of the op (DequantizeGroup: ab_scale pattern, float reference operand; DequantizeGroupRound: one
+    // rounding into A's type), each verified against its own host reference and timed
+    auto run_contract = [&](auto bop, auto bref, const char* name) {
+        using BOp = decltype(bop); using BRef = decltype(bref);
+        std::cout << "B functor: " << name << std::endl;
+        if(do_verification)
+        {
+            Tensor<BRef> b({k, n});
+            for(int i = 0; i < K; ++i) for(int j = 0; j < N; ++j) BOp{}(b(i, j), int(q(i, j)) - int(use_zp ? z(i / G, j) : 8), s(i / G, j));
+            Tensor<F32> c({m, n});
+            using Ref = ck::tensor_operation::host::ReferenceGemm<BF16, BRef, F32, F32, PassThrough, PassThrough, PassThrough>;
+            auto ref = Ref{}; auto inv = ref.MakeInvoker(); auto arg = ref.MakeArgument(a, b, c, PassThrough{}, PassThrough{}, PassThrough{});
+            inv.Run(arg);
+            for(int i = 0; i < M; ++i) for(int j = 0; j < N; ++j) PassThrough{}(e_host(i, j), c(i, j));
+        }
+        using Op = ck::tensor_operation::device::DeviceGemm_dequantB_GroupScale_Sm100<Row, Row, BF16, BF16, G, PassThrough, BOp, PassThrough>;
+        std::vector<std::unique_ptr<Op>> op_ptrs;
+        op_ptrs.push_back(std::make_unique<Op>());
+        const double bytes = 2.0 * M * K + 0.5 * N * K + 2.0 * kg * N + (use_zp ? 1.0 * kg * N : 0.0) + 2.0 * M * N;
+        return ck::profiler::run_instances(
+            op_ptrs,
+            [&](auto& op) {
+                return op.MakeArgumentPointer(a_buf.GetDeviceBuffer(), packed.GetDeviceBuffer(), s_buf.GetDeviceBuffer(), use_zp ? z_buf.GetDeviceBuffer() : nullptr,
+                                              e_buf.GetDeviceBuffer(), M, N, K, K, N, 8, PassThrough{}, BOp{}, PassThrough{});
+            },
+            [&](auto& op, auto* arg) {
+                auto ws = std::make_shared<DeviceMem>(op.GetWorkSpaceSize(arg));
+                op.SetWorkSpacePointer(arg, ws->GetDeviceBuffer());
+                return ws;
+            },
+            [&]() {
+                e_buf.FromDevice(e_dev.mData.data());
+                if(do_log) LogRangeAsType<float>(std::cout << "e_device: ", e_dev.mData, ",") << std::endl;
+                return ck::utils::check_err(e_dev, e_host, "Error: Incorrect results!", 1e-2, 1e-2);
+            },
+            do_verification, time_kernel, n_warmup, n_iter, 2.0 * M * N * K, bytes, 1.0);
+    };
+    const bool pass_f32 = run_contract(DequantizeGroup{}, F32{}, "DequantizeGroup (fp32 group scale)");
+    const bool pass_rtn = run_contract(DequantizeGroupRound{}, BF16{}, "DequantizeGroupRound (one rounding into A's type)");
+    const bool pass = pass_f32 && pass_rtn;
     return pass ? 0 : 1;
 }
 

@@ -298,7 +298,7 @@ def test_prefill_w8a16_and_w4a16_vs_oracle(M, N, K):
         q = rng.integers(0, 16, (K, N)).astype(np.uint8)
         sg = o.bf16_trunc((rng.random((K // 128, N)) * 0.015 + 0.005).astype(np.float32))
         z = rng.integers(0, 16, (K // 128, N)).astype(np.uint8)
-        got, op4 = H.run_w4a16(a, q, sg, z)
+        got, op4 = H.run_w4a16(a, q, sg, z, rtn=True)
         assert "prefill" in op4.kernel_name
         ref4 = o.gemm(a, o.BF16, q, o.U8, o.BF16, b_op=o.BOP_GROUP_RTN, scale=sg, s_dtype=o.BF16, zero=z, group_size=128)
         bad, err = H.bf16_close(got, ref4, RTOL, ATOL)
