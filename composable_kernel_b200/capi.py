@@ -26,6 +26,7 @@ ACT_PASSTHROUGH, ACT_RELU = 0, 1
 FLAG_BF16_RNE = 1
 OK, ERR_UNSUPPORTED, ERR_INVALID, ERR_NO_DEVICE, ERR_CUDA, ERR_WORKSPACE = 0, -1, -2, -3, -4, -5
 MAX_D = 2
+MAX_PEERS = 8
 
 
 class GemmProblem(C.Structure):
@@ -41,6 +42,7 @@ class GemmProblem(C.Structure):
         ("cde_op", C.c_int32), ("cde_scale", C.c_float), ("act", C.c_int32),
         ("e_dtype", C.c_int32), ("e", C.c_void_p), ("lde", C.c_int64),
         ("kbatch", C.c_int32), ("flags", C.c_uint32),
+        ("num_peers", C.c_int32), ("e_peer", C.c_void_p * MAX_PEERS), ("flag_peer", C.c_void_p * MAX_PEERS),
     ]
 
 
@@ -85,6 +87,7 @@ def lib():
         l.ckb_prepack_b_int4_bytes.restype = C.c_uint64
         l.ckb_prepack_b_int4.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_void_p,
                                          C.c_void_p]
+        l.ckb_peer_wait.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
         l.ckb_grouped_gemm_arg_bytes.argtypes = [C.c_int32, C.c_int32]
         l.ckb_grouped_gemm_arg_bytes.restype = C.c_uint64
         l.ckb_grouped_gemm_query.argtypes = [C.POINTER(GemmProblem), C.c_int32]
@@ -96,7 +99,7 @@ def lib():
 EXPORTED = [
     "ckb_gemm_query", "ckb_gemm_run", "ckb_gemm_host_staging_bytes", "ckb_gemm_run_host", "ckb_gemm_run_host_async",
     "ckb_prepack_b_u8", "ckb_prepack_b_rowmajor_i8", "ckb_prepack_b_int4_bytes", "ckb_prepack_b_int4", "ckb_grouped_gemm_run", "ckb_grouped_gemm_query", "ckb_grouped_gemm_arg_bytes",
-    "ckb_last_error", "ckb_version", "ckb_device_sm_count",
+    "ckb_last_error", "ckb_version", "ckb_device_sm_count", "ckb_peer_wait",
 ]
 
 

@@ -90,6 +90,13 @@ const char* ckb_last_error(void) { return last_error().c_str(); }
 int ckb_version(void) { return CKB_VERSION; }
 int ckb_device_sm_count(void) { return device_info().ok ? device_info().sm_count : -1; }
 
+int ckb_peer_wait(void* flag, void* epoch_state, uint32_t arrivals_per_epoch, void* stream)
+{
+    if(!flag || !epoch_state || arrivals_per_epoch == 0) return set_error(CKB_ERR_INVALID, "ckb_peer_wait: null counter or zero arrivals");
+    if(!device_info().ok) return set_error(CKB_ERR_NO_DEVICE, "no sm_100 device");
+    return launch_peer_wait(flag, epoch_state, arrivals_per_epoch, static_cast<cudaStream_t>(stream));
+}
+
 int ckb_gemm_query(const ckb_gemm_problem* pp, ckb_gemm_plan* plan)
 {
     if(!pp || !plan) return set_error(CKB_ERR_INVALID, "null problem/plan");
@@ -172,6 +179,13 @@ int ckb_gemm_query(const ckb_gemm_problem* pp, ckb_gemm_plan* plan)
     default: return unsupported(plan, "unknown b_op %d", p.b_op);
     }
     const bool w4 = p.b_op == CKB_BOP_GROUP || p.b_op == CKB_BOP_GROUP_RTN;
+    if(p.num_peers < 0 || p.num_peers > CKB_MAX_PEERS) return set_error(CKB_ERR_INVALID, "num_peers out of range");
+    if(p.num_peers > 0)
+    {
+        if(!w4 || p.M > 32) return unsupported(plan, "the fused all-gather epilogue is served by the W4A16 decode kernel (M <= 32)");
+        for(int g = 0; g < p.num_peers; ++g)
+            if(!p.e_peer[g] || !p.flag_peer[g]) return set_error(CKB_ERR_INVALID, "null peer pointer");
+    }
     if(!w4)
     {
         if(p.b_layout != CKB_COL) return unsupported(plan, "int8 B must be K-major (column-major: mk_nk_mn)");
@@ -202,7 +216,7 @@ int ckb_gemm_query(const ckb_gemm_problem* pp, ckb_gemm_plan* plan)
         // kernel (wq_gemv, <= 64 rows) wins on streaming shapes and on M > 8.  CKB_GEMV=1 / 2 forces one of them.
         const int force = getenv("CKB_GEMV") ? atoi(getenv("CKB_GEMV")) : 0;
         // RTN numerics and the fixed-K-order contract exist in the rotating-producer kernel only
-        const bool g2_only = p.b_op == CKB_BOP_GROUP_RTN || (p.flags & CKB_FLAG_FIXED_K_ORDER);
+        const bool g2_only = p.b_op == CKB_BOP_GROUP_RTN || (p.flags & CKB_FLAG_FIXED_K_ORDER) || p.num_peers > 0;
         // rows beyond 32 go through 32-row slabs: the single-producer kernel's 64-row variant (8 token tiles) is retired -- its
         // activation stage overflows the ring on K >= 4096 (mbarrier time-out found by tests/slab_probe.py)
         bool old_kernel = !g2_only && force == 1;

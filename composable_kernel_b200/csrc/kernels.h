@@ -57,6 +57,7 @@ struct G2Sched
 int schedule_wq_gemv2(int M, int N, int K, bool zp, int sms, G2Sched& s, int mode = 0);
 int plan_wq_gemv2(const ckb_gemm_problem& p, ckb_gemm_plan& plan);
 int run_wq_gemv2(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStream_t stream);
+int launch_peer_wait(void* flag, void* epoch_state, unsigned per_epoch, cudaStream_t stream);
 int plan_wq_prefill(const ckb_gemm_problem& p, ckb_gemm_plan& plan);
 int run_wq_prefill(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, void* workspace, cudaStream_t stream);
 

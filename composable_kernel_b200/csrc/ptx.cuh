@@ -226,6 +226,18 @@ __device__ __forceinline__ void named_bar_sync(uint32_t nthreads)
     asm volatile("bar.sync %0, %1;" ::"n"(ID), "r"(nthreads) : "memory");
 }
 
+// ------------------------------------------------------------------ system-scope signalling (peer GPUs over NVLink)
+__device__ __forceinline__ void red_release_sys_add_u32(unsigned* p, unsigned v)
+{
+    asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_acquire_sys_u32(const unsigned* p)
+{
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
 // ------------------------------------------------------------------ L2 cache policies
 __device__ __forceinline__ uint64_t policy_evict_first()
 {

@@ -182,6 +182,31 @@ int plan_wq_gemv2(const ckb_gemm_problem& p, ckb_gemm_plan& plan)
     return CKB_OK;
 }
 
+// consumer side of the fused all-gather (ckb_peer_wait): one thread
+static __global__ void peer_wait_kernel(const unsigned* flag, unsigned* epoch_state, unsigned per_epoch)
+{
+    ptx::pdl_launch_dependents();
+    const unsigned epoch  = *epoch_state + 1;
+    *epoch_state          = epoch;
+    const unsigned target = epoch * per_epoch;
+    while(int(ptx::ld_acquire_sys_u32(flag) - target) < 0) __nanosleep(20);
+    __threadfence_system();
+}
+
+int launch_peer_wait(void* flag, void* epoch_state, unsigned per_epoch, cudaStream_t stream)
+{
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(1); cfg.blockDim = dim3(1); cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if(cudaStreamIsCapturing(stream, &cs) != cudaSuccess) { cudaGetLastError(); cs = cudaStreamCaptureStatusNone; }
+    cfg.attrs = attr; cfg.numAttrs = cs == cudaStreamCaptureStatusActive ? 1 : 0;
+    CKB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, peer_wait_kernel, static_cast<const unsigned*>(flag), static_cast<unsigned*>(epoch_state), per_epoch));
+    return CKB_OK;
+}
+
 int run_wq_gemv2(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStream_t stream)
 {
     const G2Plan* gp = reinterpret_cast<const G2Plan*>(plan.opaque);
@@ -213,6 +238,8 @@ int run_wq_gemv2(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStrea
         a.pdl = cs == cudaStreamCaptureStatusActive;
         a.pdl = env_int("CKB_GEMV_PDL", a.pdl);
     }
+    a.num_peers = p.num_peers;
+    for(int g = 0; g < p.num_peers && g < CKB_MAX_PEERS; ++g) { a.e_peer[g] = p.e_peer[g]; a.flag_peer[g] = static_cast<unsigned*>(p.flag_peer[g]); }
     a.dbg   = env_int("CKB_GEMV_DBG", 0);
     a.trace = nullptr;
     fill_epi_params(p, a.ep);

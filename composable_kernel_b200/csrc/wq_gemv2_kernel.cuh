@@ -56,21 +56,31 @@ struct G2Args
     int pdl;        // launch with programmatic stream serialization
     int rtn;        // CKB_BOP_GROUP_RTN: (q - zp) * s rounded once into A's type before the MMA (RTN kernel instantiation)
     int dbg;        // debug knobs (CKB_GEMV_DBG): 1 = skip the math, 8 = skip the copies and waits
+    int num_peers;  // fused all-gather: > 0 = store E to e_peer[0..num_peers) and signal flag_peer[*] (ckb.h)
+    void* e_peer[CKB_MAX_PEERS];
+    unsigned* flag_peer[CKB_MAX_PEERS];
     long long* trace; // trace build: [cta][warp][10] = globaltimer at entry / prefill issued / PDL wait done / first stage full /
                       // K loop done / exit, then clock cycles waiting on full barriers / issuing refills / in the K loop / total
     EpiParams ep;
 };
 
-static __device__ __noinline__ void g2_store_one(const EpiParams& ep, int m, int n, float acc)
+static __device__ __forceinline__ void g2_store_e(const EpiParams& ep, void* e, long long off, float v)
+{
+    if(ep.e_dtype == CKB_BF16) static_cast<uint16_t*>(e)[off] = f32_to_bf16_bits(v, ep.flags);
+    else if(ep.e_dtype == CKB_F16) static_cast<__half*>(e)[off] = __float2half_rn(v);
+    else static_cast<float*>(e)[off] = v;
+}
+
+static __device__ __noinline__ void g2_store_one(const EpiParams& ep, int m, int n, float acc, int num_peers, void* const* e_peer)
 {
     float d0 = 0.f, d1 = 0.f;
     if(ep.num_d > 0) d0 = load_d_f32(ep.d_dtype[0], ep.d[0], (long long)m * ep.d_sm[0] + (long long)n * ep.d_sn[0]);
     if(ep.num_d > 1) d1 = load_d_f32(ep.d_dtype[1], ep.d[1], (long long)m * ep.d_sm[1] + (long long)n * ep.d_sn[1]);
     const float v       = cde_apply_f32(ep, acc, d0, d1);
     const long long off = (long long)m * ep.lde + n;
-    if(ep.e_dtype == CKB_BF16) static_cast<uint16_t*>(ep.e)[off] = f32_to_bf16_bits(v, ep.flags);
-    else if(ep.e_dtype == CKB_F16) static_cast<__half*>(ep.e)[off] = __float2half_rn(v);
-    else static_cast<float*>(ep.e)[off] = v;
+    if(num_peers == 0) g2_store_e(ep, ep.e, off, v);
+    else
+        for(int g = 0; g < num_peers; ++g) g2_store_e(ep, e_peer[g], off, v); // this rank's slot in every rank's gathered buffer
 }
 
 #ifdef CKB_ENABLE_TRACE
@@ -368,7 +378,7 @@ wq_gemv2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                     red[warp * n_vec + (gi * NT + nt) * 32 + lane] =
                         make_float4(acc[gi][nt][0], acc[gi][nt][1], acc[gi][nt][2], acc[gi][nt][3]);
         __syncthreads();
-        const bool fast = ep.cde_op == CKB_CDE_PASSTHROUGH && (ep.e_dtype == CKB_BF16 || ep.e_dtype == CKB_F16);
+        const bool fast = ep.cde_op == CKB_CDE_PASSTHROUGH && (ep.e_dtype == CKB_BF16 || ep.e_dtype == CKB_F16) && args.num_peers == 0;
         // thread -> (half h, vector v): the WK partial sums of a vector are added and stored by one thread
         const int n_out = sg * NT * 32;
         for(int o = tid; o < n_out; o += NW * 32)
@@ -396,14 +406,26 @@ wq_gemv2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                         static_cast<uint16_t*>(ep.e)[(long long)m * ep.lde + n] =
                             ep.e_dtype == CKB_BF16 ? f32_to_bf16_bits(vv[r], ep.flags) : __half_as_ushort(__float2half_rn(vv[r]));
                     else
-                        g2_store_one(ep, m, n, vv[r]);
+                        g2_store_one(ep, m, n, vv[r], args.num_peers, args.e_peer);
                 }
             }
+        }
+    }
+    if(args.num_peers > 0)
+    {
+        // fused all-gather: every store of this CTA is ordered before its arrival on every rank's counter (CTA barrier, then
+        // one thread: system-scope fence + release adds over NVLink); the consumer side is ckb_peer_wait
+        __syncthreads();
+        if(threadIdx.x < args.num_peers)
+        {
+            __threadfence_system();
+            ptx::red_release_sys_add_u32(args.flag_peer[threadIdx.x], 1u);
         }
     }
     G2_T(5);
     G2_TV(9, clock64() - clk_entry);
 }
+
 
 struct G2Plan
 {

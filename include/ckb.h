@@ -106,6 +106,7 @@ enum {
 };
 
 #define CKB_MAX_D 2
+#define CKB_MAX_PEERS 8
 
 /* E[M,N] = cde( A[M,K] * bop(B[K,N], scale[, zero]), D0, D1 ) */
 typedef struct ckb_gemm_problem {
@@ -147,6 +148,17 @@ typedef struct ckb_gemm_problem {
 
     int32_t kbatch; /* split-K hint (KBatch / KSplit of DeviceGemmV2R1); 0 or 1 = library decides */
     uint32_t flags;
+
+    /* [EXT] fused all-gather of the output over NVLink peer memory (column-parallel shards across the GPUs of one box,
+       SURVEY.md 8e; the reference has no multi-GPU code).  num_peers = G > 0: the epilogue stores every element of this
+       rank's E slice at e_peer[g][m*lde + n] for g = 0..G-1 -- e_peer[g] is THIS rank's slot inside rank g's gathered
+       buffer, a peer-mapped device pointer (cudaIpc / cuMem / torch symmetric memory), own rank included; `e` is not
+       written.  After its stores every CTA adds 1 (release, system scope) to the uint32 arrival counter flag_peer[g] of
+       every rank; a rank's gathered buffer is complete when its counter has grown by plan.grid * G (ckb_peer_wait).
+       Served by the W4A16 decode kernel (M <= 32, GROUP / GROUP_RTN); other problems report unsupported. */
+    int32_t num_peers;
+    void* e_peer[CKB_MAX_PEERS];
+    void* flag_peer[CKB_MAX_PEERS];
 } ckb_gemm_problem;
 
 typedef struct ckb_gemm_plan {
@@ -223,6 +235,12 @@ int ckb_grouped_gemm_query(const ckb_gemm_problem* proto, int32_t group_count);
    M of every group is read on the device; sum_m (gemm_descs[i].M_ == sum of all M, :460-463) sizes the grid. */
 int ckb_grouped_gemm_run(const ckb_gemm_problem* proto, const void* dev_args, int32_t group_count,
                          int32_t sum_m, void* stream);
+
+/* [EXT] consumer side of the fused all-gather: enqueue a one-thread kernel on `stream` that advances the epoch counter
+   *epoch_state (device uint32, starts at 0) and returns once *flag (this rank's arrival counter, device uint32, starts
+   at 0) has reached epoch * arrivals_per_epoch.  Everything enqueued on `stream` after it sees the gathered buffer.
+   Graph-capturable (all state lives in device memory). */
+int ckb_peer_wait(void* flag, void* epoch_state, uint32_t arrivals_per_epoch, void* stream);
 
 /* ---- misc --------------------------------------------------------------------------------- */
 const char* ckb_last_error(void);

@@ -22,6 +22,61 @@ def w4_op(a, packed, sc, z, e, N, K):
                       N=N, K=K, scale=sc, zero=z, zero_const=8, group_size=128, flags=capi.FLAG_FIXED_K_ORDER)
 
 
+def fused_gather_cases(rank, world, dev):
+    """Fused all-gather (epilogue stores into every rank's buffer over NVLink + ckb_peer_wait) against the NCCL gather of the
+    same slices, eager and under CUDA-graph replay with rotating buffers."""
+    bad = 0
+    for M, N, K in [(1, 28672, 8192), (16, 28672, 8192), (4, 4096, 4096)]:
+        if not shard.equal_shards(N, world, 16):
+            continue
+        n_loc = N // world
+        g = torch.Generator(device=dev)
+        g.manual_seed(99 + M)
+        a = torch.randn(M, K, device=dev, generator=g).bfloat16()
+        packed = torch.randint(0, 256, (int(capi.lib().ckb_prepack_b_int4_bytes(N, K)),), dtype=torch.uint8, device=dev, generator=g)
+        sc = (torch.rand(K // 128, N, device=dev, generator=g) * 0.015 + 0.005).bfloat16()
+        per_group = (K // 64) * 512
+        p_loc = packed[(rank * n_loc // 16) * per_group:((rank + 1) * n_loc // 16) * per_group].clone()
+        s_loc = sc[:, rank * n_loc:(rank + 1) * n_loc].contiguous()
+        e_loc = torch.zeros(M, n_loc, dtype=torch.bfloat16, device=dev)
+        ref_op = ops.GemmOp(a, p_loc, e_loc, b_dtype=capi.I4, b_layout=capi.PREPACKED, b_op=capi.BOP_GROUP, N=n_loc, K=K, scale=s_loc,
+                            zero_const=8, group_size=128, flags=capi.FLAG_FIXED_K_ORDER)
+        ref_op.run()
+        torch.cuda.synchronize()
+        want = shard.all_gather_columns(e_loc, world, row_major=False)        # NCCL reference: E_all[G][M][n_loc]
+        pg = shard.PeerGather(M, n_loc, world, rank, torch.bfloat16, slots=2)
+        opsl = [ops.GemmOp(a, p_loc, e_loc, b_dtype=capi.I4, b_layout=capi.PREPACKED, b_op=capi.BOP_GROUP, N=n_loc, K=K, scale=s_loc,
+                           zero_const=8, group_size=128, flags=capi.FLAG_FIXED_K_ORDER, e_peers=pg.e_peers(s), flag_peers=pg.flag_peers())
+                for s in range(2)]
+        assert all(o.supported for o in opsl), opsl[0].why
+        st = torch.cuda.Stream()
+        with torch.cuda.stream(st):
+            for s in range(2):                                               # eager: one step per slot
+                opsl[s].run(st.cuda_stream)
+                pg.wait(opsl[s].plan.grid, st.cuda_stream)
+            torch.cuda.synchronize()
+            ok_eager = all(torch.equal(pg.gathered(s).view(torch.int16), want.view(torch.int16)) for s in range(2))
+            dist.barrier()
+            pg.buf[shard.PeerGather.HEADER:].zero_()
+            torch.cuda.synchronize()
+            dist.barrier()
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr, stream=st):
+                for rep in range(4):
+                    for s in range(2):
+                        opsl[s].run(st.cuda_stream)
+                        pg.wait(opsl[s].plan.grid, st.cuda_stream)
+            for _ in range(3):
+                gr.replay()
+            torch.cuda.synchronize()
+            ok_graph = all(torch.equal(pg.gathered(s).view(torch.int16), want.view(torch.int16)) for s in range(2))
+            dist.barrier()
+        print(f"rank {rank}/{world} fused-gather M{M} N{N} K{K}: eager {ok_eager} graph-replay {ok_graph} kernel {opsl[0].kernel_name}", flush=True)
+        bad += 0 if (ok_eager and ok_graph) else 1
+        del pg, gr
+    return bad
+
+
 def main():
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
@@ -72,6 +127,7 @@ def main():
             bad += 1
         del packed, p_loc, e_full, e_all, blocked
         torch.cuda.empty_cache()
+    bad += fused_gather_cases(rank, world, dev)
     t = torch.tensor([bad], device=dev)
     dist.all_reduce(t)
     dist.destroy_process_group()
