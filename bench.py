@@ -568,7 +568,7 @@ def cfg5_sharded(torch, dist, capi, ops, dev, rank, world):
         shards.append((packed[g0 * per_group:(g0 + n_loc // 16) * per_group].clone(), sc[:, rank * n_loc:(rank + 1) * n_loc].contiguous()))
         del packed, sc
     torch.cuda.empty_cache()
-    out = {"N": N, "K": K, "world": world, "scaling": "strong", "launch": "cuda-graph replay incl. the NCCL all-gather", "M": {}}
+    out = {"N": N, "K": K, "world": world, "scaling": "strong", "launch": "cuda-graph replay incl. the gather (gemm_gather_us: NCCL all_gather_into_tensor in the graph; gemm_fused_gather_us: epilogue peer stores + ckb_peer_wait, no collective call)", "M": {}}
     st = torch.cuda.Stream(device=dev)
     for M in (1, 16, 4096):
         a = torch.randn(M, K, device=dev, generator=gen).bfloat16()
@@ -605,6 +605,43 @@ def cfg5_sharded(torch, dist, capi, ops, dev, rank, world):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             res["gemm_gather_us" if gather else "gemm_us"] = round(float(t.item()), 2)
             del g
+        if M <= 32:
+            # fused form: the epilogue stores the slice into every rank's gathered buffer over NVLink peer memory and the
+            # step ends with ckb_peer_wait (no collective call); buffers rotate over two slots (shard.PeerGather)
+            from composable_kernel_b200 import shard as _shard
+            pg = _shard.PeerGather(M, n_loc, world, rank, torch.bfloat16, slots=2)
+            fl = [ops.GemmOp(a, p, e_loc[0], b_dtype=capi.I4, b_layout=capi.PREPACKED, b_op=capi.BOP_GROUP, N=n_loc, K=K, scale=s,
+                             zero_const=8, group_size=GROUP, e_peers=pg.e_peers(i % 2), flag_peers=pg.flag_peers(), peer_rank=rank)
+                  for i, (p, s) in enumerate(shards)]
+            n_f = len(fl) // 2 * 2
+            with torch.cuda.stream(st):
+                def run_fused():
+                    for op in fl[:n_f]:
+                        op.run(st.cuda_stream)
+                        pg.wait(op.plan.grid, st.cuda_stream)
+                run_fused()
+                torch.cuda.synchronize()
+                dist.barrier()
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=st):
+                    run_fused()
+                g.replay()
+                torch.cuda.synchronize()
+                dist.barrier()
+                t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                t0.record(st)
+                for _ in range(3):
+                    g.replay()
+                t1.record(st)
+                torch.cuda.synchronize()
+                dist.barrier()
+            t = torch.tensor([t0.elapsed_time(t1) * 1e3 / (3 * n_f)], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            res["gemm_fused_gather_us"] = round(float(t.item()), 2)
+            res["fused_kernel"] = fl[0].kernel_name
+            res["fused_gather_over_gemm"] = round(res["gemm_us"] / res["gemm_fused_gather_us"], 3)
+            res["gbps_gemm_fused_gather"] = round(algo_bytes(M, N, K) / res["gemm_fused_gather_us"] / 1e3, 1)
+            del g, fl, pg
         gbytes = 2 * M * N  # bytes every rank holds after the gather
         res["tflops_gemm"] = round(2 * M * N * K / res["gemm_us"] / 1e6, 2)
         res["tflops_gemm_gather"] = round(2 * M * N * K / res["gemm_gather_us"] / 1e6, 2)

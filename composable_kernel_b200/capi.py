@@ -42,7 +42,7 @@ class GemmProblem(C.Structure):
         ("cde_op", C.c_int32), ("cde_scale", C.c_float), ("act", C.c_int32),
         ("e_dtype", C.c_int32), ("e", C.c_void_p), ("lde", C.c_int64),
         ("kbatch", C.c_int32), ("flags", C.c_uint32),
-        ("num_peers", C.c_int32), ("e_peer", C.c_void_p * MAX_PEERS), ("flag_peer", C.c_void_p * MAX_PEERS),
+        ("num_peers", C.c_int32), ("peer_rank", C.c_int32), ("e_peer", C.c_void_p * MAX_PEERS), ("flag_peer", C.c_void_p * MAX_PEERS),
     ]
 
 

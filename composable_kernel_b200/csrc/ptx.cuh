@@ -231,6 +231,18 @@ __device__ __forceinline__ void red_release_sys_add_u32(unsigned* p, unsigned v)
 {
     asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+__device__ __forceinline__ unsigned atom_acq_rel_gpu_add_u32(unsigned* p, unsigned v)
+{
+    unsigned old;
+    asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+    return old;
+}
+__device__ __forceinline__ unsigned ld_relaxed_sys_u32(const unsigned* p)
+{
+    unsigned v;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 __device__ __forceinline__ unsigned ld_acquire_sys_u32(const unsigned* p)
 {
     unsigned v;

@@ -189,8 +189,10 @@ static __global__ void peer_wait_kernel(const unsigned* flag, unsigned* epoch_st
     const unsigned epoch  = *epoch_state + 1;
     *epoch_state          = epoch;
     const unsigned target = epoch * per_epoch;
-    while(int(ptx::ld_acquire_sys_u32(flag) - target) < 0) __nanosleep(20);
-    __threadfence_system();
+    // poll with relaxed loads (a system-scope acquire costs microseconds per iteration), then ONE acquire load pairs with the
+    // producers' release adds
+    while(int(ptx::ld_relaxed_sys_u32(flag) - target) < 0) { }
+    (void)ptx::ld_acquire_sys_u32(flag);
 }
 
 int launch_peer_wait(void* flag, void* epoch_state, unsigned per_epoch, cudaStream_t stream)
@@ -239,6 +241,7 @@ int run_wq_gemv2(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStrea
         a.pdl = env_int("CKB_GEMV_PDL", a.pdl);
     }
     a.num_peers = p.num_peers;
+    a.peer_rank = p.peer_rank;
     for(int g = 0; g < p.num_peers && g < CKB_MAX_PEERS; ++g) { a.e_peer[g] = p.e_peer[g]; a.flag_peer[g] = static_cast<unsigned*>(p.flag_peer[g]); }
     a.dbg   = env_int("CKB_GEMV_DBG", 0);
     a.trace = nullptr;

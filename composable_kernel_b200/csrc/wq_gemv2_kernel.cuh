@@ -56,6 +56,7 @@ struct G2Args
     int pdl;        // launch with programmatic stream serialization
     int rtn;        // CKB_BOP_GROUP_RTN: (q - zp) * s rounded once into A's type before the MMA (RTN kernel instantiation)
     int dbg;        // debug knobs (CKB_GEMV_DBG): 1 = skip the math, 8 = skip the copies and waits
+    int peer_rank;  // this rank's index among the peers
     int num_peers;  // fused all-gather: > 0 = store E to e_peer[0..num_peers) and signal flag_peer[*] (ckb.h)
     void* e_peer[CKB_MAX_PEERS];
     unsigned* flag_peer[CKB_MAX_PEERS];
@@ -406,21 +407,28 @@ wq_gemv2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                         static_cast<uint16_t*>(ep.e)[(long long)m * ep.lde + n] =
                             ep.e_dtype == CKB_BF16 ? f32_to_bf16_bits(vv[r], ep.flags) : __half_as_ushort(__float2half_rn(vv[r]));
                     else
-                        g2_store_one(ep, m, n, vv[r], args.num_peers, args.e_peer);
+                        g2_store_one(ep, m, n, vv[r], (args.dbg & 32) ? 1 : args.num_peers, (args.dbg & 32) ? &args.e_peer[args.peer_rank] : args.e_peer);
                 }
             }
         }
     }
-    if(args.num_peers > 0)
+    if(args.num_peers > 0 && !(args.dbg & 128))
     {
         // fused all-gather: every store of this CTA is ordered before its arrival on every rank's counter (CTA barrier, then
         // one thread: system-scope fence + release adds over NVLink); the consumer side is ckb_peer_wait
+        // (a system-scope release costs ~2.5 us on this part, tests/peer_probe.py, so only the LAST CTA of the grid pays it: CTAs
+        // count themselves on a device-scope counter next to this rank's own flag word; the one that completes the grid
+        // publishes one arrival per rank)
+        volatile int* s_last_p = reinterpret_cast<volatile int*>(smem); // the ring is drained: its first word carries the verdict
         __syncthreads();
-        if(threadIdx.x < args.num_peers)
+        if(threadIdx.x == 0)
         {
-            __threadfence_system();
-            ptx::red_release_sys_add_u32(args.flag_peer[threadIdx.x], 1u);
+            const unsigned old = ptx::atom_acq_rel_gpu_add_u32(args.flag_peer[args.peer_rank] + 1, 1u);
+            *s_last_p = ((old + 1u) % gridDim.x) == 0u;
         }
+        __syncthreads();
+        if(*s_last_p && threadIdx.x < args.num_peers)
+            ptx::red_release_sys_add_u32(args.flag_peer[(args.dbg & 64) ? args.peer_rank : threadIdx.x], 1u);
     }
     G2_T(5);
     G2_TV(9, clock64() - clk_entry);

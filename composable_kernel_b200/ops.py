@@ -29,7 +29,7 @@ class GemmOp:
     def __init__(self, a, b, e, *, b_dtype=None, b_layout=capi.COL, b_op=capi.BOP_PASSTHROUGH,
                  N=None, K=None, ldb=None, scale=None, zero=None, zero_const=8, group_size=0,
                  ds=(), d_strides=(), cde_op=capi.CDE_PASSTHROUGH, cde_scale=1.0,
-                 act=capi.ACT_PASSTHROUGH, flags=0, kbatch=0, e_peers=None, flag_peers=None):
+                 act=capi.ACT_PASSTHROUGH, flags=0, kbatch=0, e_peers=None, flag_peers=None, peer_rank=0):
         """a: [M,K] row-major (stride(1)==1).  b: weight storage tensor; for COL layout a [N,K] tensor
         (K contiguous), for PREPACKED a flat uint8 tensor from prepack_int4 (then N,K are required).
         e: [M,N] row-major output.  ds: D tensors with explicit (stride_m, stride_n) element strides."""
@@ -61,7 +61,7 @@ class GemmOp:
         p.kbatch, p.flags = kbatch, flags
         if e_peers:
             # fused all-gather epilogue: raw peer-mapped pointers (this rank's slot in every rank's buffer, every rank's counter)
-            p.num_peers = len(e_peers)
+            p.num_peers, p.peer_rank = len(e_peers), peer_rank
             for g, (ep_, fp_) in enumerate(zip(e_peers, flag_peers)):
                 p.e_peer[g], p.flag_peer[g] = int(ep_), int(fp_)
         self.problem = p

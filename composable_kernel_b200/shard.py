@@ -54,7 +54,7 @@ class PeerGather:
     counter (ckb_gemm_problem.e_peer / flag_peer); `wait()` enqueues ckb_peer_wait, after which the local E_all is
     complete.  Buffers rotate over `slots` >= 2 so that a rank running one step ahead never overwrites a buffer a slower
     rank still reads (a rank can only enter step i + 2 after every rank signalled step i + 1, i.e. finished reading i)."""
-    HEADER = 256  # bytes: uint32 arrival counter at 0, uint32 epoch at 128
+    HEADER = 256  # bytes: uint32 arrival counter at 0, the kernels' scratch word at 4, uint32 epoch at 128
 
     def __init__(self, M: int, n_loc: int, world: int, rank: int, dtype, slots: int = 2, group=None):
         import torch
@@ -88,7 +88,7 @@ class PeerGather:
         return self.buf[o:o + n].view(self.dtype).view(self.world, self.M, self.n_loc)
 
     def wait(self, grid: int, stream) -> None:
-        """enqueue the consumer-side wait for one step in which every rank launched `grid` CTAs"""
+        """enqueue the consumer-side wait for one step (one arrival per rank; `grid` is kept for callers' bookkeeping)"""
         from . import capi
         base = self.buf.data_ptr()
-        capi.check(capi.lib().ckb_peer_wait(base, base + 128, grid * self.world, stream))
+        capi.check(capi.lib().ckb_peer_wait(base, base + 128, self.world, stream))

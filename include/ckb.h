@@ -153,10 +153,12 @@ typedef struct ckb_gemm_problem {
        SURVEY.md 8e; the reference has no multi-GPU code).  num_peers = G > 0: the epilogue stores every element of this
        rank's E slice at e_peer[g][m*lde + n] for g = 0..G-1 -- e_peer[g] is THIS rank's slot inside rank g's gathered
        buffer, a peer-mapped device pointer (cudaIpc / cuMem / torch symmetric memory), own rank included; `e` is not
-       written.  After its stores every CTA adds 1 (release, system scope) to the uint32 arrival counter flag_peer[g] of
-       every rank; a rank's gathered buffer is complete when its counter has grown by plan.grid * G (ckb_peer_wait).
+       written.  flag_peer[g] points to TWO uint32 in rank g's memory: [0] the arrival counter, [1] a scratch word only rank
+       g's own kernels touch (both start at 0).  When the last CTA of the launch has finished (device-scope count on the own
+       scratch word) it adds 1 (release, system scope) to the arrival counter of every rank; a rank's gathered buffer is
+       complete when its counter has grown by G (ckb_peer_wait).  peer_rank = this rank's index in the arrays.
        Served by the W4A16 decode kernel (M <= 32, GROUP / GROUP_RTN); other problems report unsupported. */
-    int32_t num_peers;
+    int32_t num_peers, peer_rank;
     void* e_peer[CKB_MAX_PEERS];
     void* flag_peer[CKB_MAX_PEERS];
 } ckb_gemm_problem;

@@ -46,7 +46,7 @@ def fused_gather_cases(rank, world, dev):
         want = shard.all_gather_columns(e_loc, world, row_major=False)        # NCCL reference: E_all[G][M][n_loc]
         pg = shard.PeerGather(M, n_loc, world, rank, torch.bfloat16, slots=2)
         opsl = [ops.GemmOp(a, p_loc, e_loc, b_dtype=capi.I4, b_layout=capi.PREPACKED, b_op=capi.BOP_GROUP, N=n_loc, K=K, scale=s_loc,
-                           zero_const=8, group_size=128, flags=capi.FLAG_FIXED_K_ORDER, e_peers=pg.e_peers(s), flag_peers=pg.flag_peers())
+                           zero_const=8, group_size=128, flags=capi.FLAG_FIXED_K_ORDER, e_peers=pg.e_peers(s), flag_peers=pg.flag_peers(), peer_rank=rank)
                 for s in range(2)]
         assert all(o.supported for o in opsl), opsl[0].why
         st = torch.cuda.Stream()
