@@ -5,7 +5,7 @@
 // sm_100a operator that chooses its kernel per problem at run time.
 #pragma once
 #include "ck/library/tensor_operation_instance/device_operation_instance_factory.hpp"
-#include "ck/tensor_operation/gpu/device/impl/device_gemm_sm100.hpp"
+#include "ck/tensor_operation/gpu/device/impl/device_gemm_multiple_abd_xdl_cshuffle.hpp"
 
 namespace ck {
 namespace tensor_operation {

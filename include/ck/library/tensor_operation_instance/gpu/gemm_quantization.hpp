@@ -3,7 +3,7 @@
 //  .../gpu/gemm_multiply_multiply.hpp:20-215 -- the reference wires fp8 only; int8 is the [EXT] dtype of cfg4).
 #pragma once
 #include "ck/library/tensor_operation_instance/device_operation_instance_factory.hpp"
-#include "ck/tensor_operation/gpu/device/impl/device_gemm_sm100.hpp"
+#include "ck/tensor_operation/gpu/device/impl/device_gemm_multiple_d_xdl_cshuffle.hpp"
 
 namespace ck {
 namespace tensor_operation {

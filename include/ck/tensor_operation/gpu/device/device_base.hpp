@@ -1,6 +1,7 @@
 // ck/tensor_operation/gpu/device/device_base.hpp -- BaseArgument / BaseInvoker / BaseOperator with the
 // reference's exact surface (include/ck/tensor_operation/gpu/device/device_base.hpp:15-71).
 #pragma once
+#include "ck/ck.hpp"
 #include <cassert>
 #include <sstream>
 #include <string>

@@ -9,6 +9,7 @@
 #pragma once
 #include <cuda_runtime_api.h>
 
+#include <algorithm>
 #include <cstdio>
 #include <memory>
 #include <stdexcept>
@@ -16,6 +17,8 @@
 #include <type_traits>
 #include <utility>
 
+#include "ck/host_utility/flush_cache.hpp"
+#include "ck/host_utility/kernel_launch.hpp"
 #include "ck/tensor_operation/gpu/device/device_base.hpp"
 #include "ck/tensor_operation/gpu/device/tensor_layout.hpp"
 #include "ck/tensor_operation/gpu/element/element_wise_operation.hpp"
@@ -56,6 +59,13 @@ inline void cuda_check(cudaError_t e, const char* what)
     if(e != cudaSuccess) throw std::runtime_error(std::string(what) + ": " + cudaGetErrorString(e));
 }
 
+// name of the kernel chosen by the most recent ckb_gemm_query of this thread (for GetTypeString)
+inline std::string& last_kernel_name()
+{
+    static thread_local std::string s;
+    return s;
+}
+
 // Common Argument: owns the POD problem and the plan.
 struct GemmArgument : public BaseArgument
 {
@@ -66,7 +76,36 @@ struct GemmArgument : public BaseArgument
     // The reference ops on this path need no caller workspace (GetWorkSpaceSize() == 0 there); the stream-K
     // kernels do, so when the caller has not supplied one the argument owns a small zeroed buffer.
     std::shared_ptr<void> own_workspace;
-    std::shared_ptr<void> own_b; // K-major copy of a row-major weight (see DeviceGemmMultipleABD_Xdl_CShuffle)
+    // Row-major int8 B (CK's mk_kn_mn): the kernels stream K-major weights, so the op needs N*K bytes for a K-major copy.
+    // MakeArgument has no side effects (as in the reference): it only records the request and validates the problem.  The
+    // bytes are reported by GetWorkSpaceSize and taken through SetWorkSpacePointer (device_base.hpp:60-68), which enqueues
+    // the transpose on the StreamConfig's stream -- a snapshot of the weight at that moment: call SetWorkSpacePointer again
+    // after changing B.  A client that never supplies a workspace (the reference's client_example/30 does not) still runs:
+    // the first Run allocates the copy itself and transposes on the run stream (not graph-capturable; documented fallback).
+    const void* rowmajor_b = nullptr;
+    int64_t rowmajor_ld    = 0;
+    bool b_ready           = true;
+    std::shared_ptr<void> own_b;
+    static size_t Align256(size_t v) { return (v + 255) / 256 * 256; }
+    size_t RepackBytes() const { return rowmajor_b ? Align256(size_t(problem.N) * problem.K) : 0; }
+    void DeferRowMajorB()
+    {
+        rowmajor_b  = problem.b;
+        rowmajor_ld = problem.ldb;
+        b_ready     = false;
+        // validate / plan as the K-major problem it will become (the pointer is replaced once the copy exists)
+        problem.ldb = problem.K; problem.b_layout = CKB_COL;
+        if(rowmajor_ld < problem.N) { why = "StrideB < N"; return; }
+        Query();
+    }
+    void PrepareB(void* dst, cudaStream_t stream)
+    {
+        if(ckb_prepack_b_rowmajor_i8(rowmajor_b, rowmajor_ld, problem.K, problem.N, dst, stream) != CKB_OK)
+            throw std::runtime_error(std::string("ckb_prepack_b_rowmajor_i8: ") + ckb_last_error());
+        problem.b = dst;
+        Query(); // tensor maps for the final pointer
+        b_ready = true;
+    }
     void* Workspace()
     {
         if(p_workspace_ || plan.workspace_bytes == 0) return p_workspace_;
@@ -86,6 +125,18 @@ struct GemmArgument : public BaseArgument
         queried      = true;
         if(rc != CKB_OK || !plan.supported) why = ckb_last_error();
         if(rc != CKB_OK) plan.supported = 0;
+        if(plan.supported) last_kernel_name() = plan.kernel_name;
+    }
+    // bytes of the A and B buffers (for the rotating copies of flush_cache.hpp)
+    size_t SizeA() const
+    {
+        const size_t eb = (problem.a_dtype == CKB_I8 || problem.a_dtype == CKB_U8) ? 1 : 2;
+        return size_t(problem.M) * size_t(problem.lda) * eb;
+    }
+    size_t SizeB() const
+    {
+        if(problem.b_layout == CKB_PREPACKED) return size_t(ckb_prepack_b_int4_bytes(problem.N, problem.K));
+        return size_t(problem.N) * size_t(problem.ldb);
     }
     void Print() const
     {
@@ -101,45 +152,56 @@ struct GemmInvoker : public BaseInvoker
         if(!arg.plan.supported)
             throw std::runtime_error("wrong! the device op does not support this GEMM problem: " + arg.why);
         if(sc.log_level_ > 0 || EnvIsEnabled("CK_LOGGING")) arg.Print();
+        if(!arg.b_ready)
+        {
+            auto& a = const_cast<GemmArgument&>(arg);
+            void* t = nullptr;
+            cuda_check(cudaMalloc(&t, a.RepackBytes()), "cudaMalloc(K-major copy of B; supply a workspace to avoid this)");
+            a.own_b = std::shared_ptr<void>(t, [](void* q) { cudaFree(q); });
+            a.PrepareB(t, sc.stream_id_);
+        }
         auto launch = [&]() {
             const int rc = ckb_gemm_run(&arg.problem, &arg.plan, const_cast<GemmArgument&>(arg).Workspace(), sc.stream_id_);
             if(rc != CKB_OK) throw std::runtime_error(std::string("ckb_gemm_run: ") + ckb_last_error());
         };
-        if(!sc.time_kernel_)
+        if(sc.flush_cache)
         {
-            launch();
-            return 0.f;
+            // cold-cache timing (flush_cache.hpp): rotating copies of A and B, L2 evicted before every timed launch, median
+            auto& a = const_cast<GemmArgument&>(arg);
+            utility::RotatingMem rot(a.problem.a, a.problem.b, a.SizeA(), a.SizeB(), std::size_t(std::max(1, sc.rotating_count)),
+                                     [&](const void* pa, const void* pb) { a.problem.a = pa; a.problem.b = pb; a.Query(); });
+            if(sc.log_level_ > 0 || EnvIsEnabled("CK_LOGGING")) rot.Print();
+            auto pre = [&]() { rot.Next(); utility::flush_cache(sc.stream_id_); };
+            return utility::launch_and_time_kernel_with_preprocess<false>(sc, pre, launch);
         }
-        // launch_and_time_kernel (kernel_launch.hpp:37-69): warm-ups, then nrepeat launches between two events
-        for(int i = 0; i < sc.cold_niters_; ++i) launch();
-        cudaEvent_t start, stop;
-        cuda_check(cudaEventCreate(&start), "cudaEventCreate");
-        cuda_check(cudaEventCreate(&stop), "cudaEventCreate");
-        cuda_check(cudaDeviceSynchronize(), "cudaDeviceSynchronize");
-        cuda_check(cudaEventRecord(start, sc.stream_id_), "cudaEventRecord");
-        for(int i = 0; i < sc.nrepeat_; ++i) launch();
-        cuda_check(cudaEventRecord(stop, sc.stream_id_), "cudaEventRecord");
-        cuda_check(cudaEventSynchronize(stop), "cudaEventSynchronize");
-        float ms = 0.f;
-        cuda_check(cudaEventElapsedTime(&ms, start, stop), "cudaEventElapsedTime");
-        cudaEventDestroy(start);
-        cudaEventDestroy(stop);
-        return ms / float(sc.nrepeat_);
+        // launch_and_time_kernel (kernel_launch.hpp:37-69): warm-ups, then nrepeat launches between two events, mean
+        return launch_and_time_kernel(sc, launch);
     }
     float Run(const BaseArgument* p_arg, const StreamConfig& sc = StreamConfig{}) override
     {
-        return Run(*dynamic_cast<const GemmArgument*>(p_arg), sc);
+        const auto* a = dynamic_cast<const GemmArgument*>(p_arg);
+        if(!a) throw std::runtime_error("wrong! the argument was not made by this device operation");
+        return Run(*a, sc);
     }
 };
 
 // Workspace handling shared by every op: GetWorkSpaceSize = plan.workspace_bytes; SetWorkSpacePointer zeroes
 // it once (the kernels keep the stream-K workspace zero between launches).
-inline size_t workspace_size(const BaseArgument* p) { return size_t(dynamic_cast<const GemmArgument*>(p)->plan.workspace_bytes); }
+inline size_t workspace_size(const BaseArgument* p)
+{
+    const auto* a = dynamic_cast<const GemmArgument*>(p);
+    if(!a) return 0;
+    const size_t kbytes = size_t(a->plan.workspace_bytes); // stream-K partial sums (decode-shaped int8-weight problems)
+    return a->rowmajor_b ? GemmArgument::Align256(kbytes) + a->RepackBytes() : kbytes;
+}
 inline void set_workspace(BaseArgument* p_arg, void* p_workspace, const StreamConfig& sc)
 {
     p_arg->p_workspace_ = p_workspace;
-    const size_t bytes  = workspace_size(p_arg);
-    if(p_workspace && bytes) cuda_check(cudaMemsetAsync(p_workspace, 0, bytes, sc.stream_id_), "cudaMemsetAsync(workspace)");
+    auto* a = dynamic_cast<GemmArgument*>(p_arg);
+    if(!a || !p_workspace) return;
+    const size_t kbytes = size_t(a->plan.workspace_bytes);
+    if(kbytes) cuda_check(cudaMemsetAsync(p_workspace, 0, kbytes, sc.stream_id_), "cudaMemsetAsync(workspace)");
+    if(a->rowmajor_b) a->PrepareB(static_cast<char*>(p_workspace) + GemmArgument::Align256(kbytes), sc.stream_id_);
 }
 
 template <typename Op, typename = void>

@@ -5,10 +5,12 @@
 //   DeviceGemmMultipleABD_Xdl_CShuffle     device/impl/device_gemm_multiple_abd_xdl_cshuffle.hpp:71-747
 //   DeviceGemmMultipleD_Xdl_CShuffle       device/impl/device_gemm_multiple_d_xdl_cshuffle.hpp
 //   DeviceGemmMultiD_Xdl_CShuffle_V3       device/impl/device_gemm_multiple_d_xdl_cshuffle_v3.hpp:143-175
-// The reference's trailing tile-shape / vector-width template parameters do not exist here: one class serves
-// every shape and picks the sm_100a kernel (decode stream-K vs. persistent tiles) at run time through
-// ckb_gemm_query.  `typename... Unused` swallows type-valued tuning arguments so that most instance
-// declarations still compile; integer tuning arguments must be dropped.
+// This header holds the implementations (`*_Sm100`: type parameters + GemmSpec only -- one class serves every shape and picks
+// the sm_100a kernel at run time through ckb_gemm_query).  The classes with the REFERENCE names and the reference's full
+// template parameter lists (tile shapes, vector widths, pipeline enums: accepted, named, ignored) live in the headers of the
+// same names as upstream -- device_fpAintB_gemm_wmma.hpp, device_gemm_multiple_abd_xdl_cshuffle.hpp,
+// device_gemm_multiple_d_xdl_cshuffle.hpp, device_gemm_multiple_d_xdl_cshuffle_v3.hpp -- and derive from these, so that the
+// reference's own instance declarations compile unchanged (tests/cpp/verbatim_instances.cpp).
 #pragma once
 #include <array>
 
@@ -34,11 +36,21 @@ inline void fill_d(ckb_gemm_problem& p, const std::array<const void*, N>& ptrs, 
         fill_d<DsLayout, DsDataType, I + 1, N>(p, ptrs, strides);
     }
 }
-inline std::string type_string(const char* cls, const GemmArgument* a)
+// GetTypeString(): reference class name + the sm_100a kernel the most recent MakeArgument of this thread selected (the op
+// object itself is stateless, as in the reference; the kernel is chosen per problem)
+inline std::string type_string(const char* cls, const GemmArgument* a = nullptr)
 {
     std::string s = std::string(cls) + "<sm_100a";
-    if(a && a->queried) s += std::string(", ") + a->plan.kernel_name;
+    const std::string& k = (a && a->queried) ? std::string(a->plan.kernel_name) : last_kernel_name();
+    if(!k.empty()) s += ", " + k;
     return s + ">";
+}
+// null-safe downcast of the type-erased argument (the reference dereferences dynamic_cast unchecked)
+inline const GemmArgument& checked(const BaseArgument* p)
+{
+    const auto* a = dynamic_cast<const GemmArgument*>(p);
+    if(!a) throw std::runtime_error("wrong! the argument was not made by this device operation");
+    return *a;
 }
 } // namespace ckb_detail
 
@@ -47,8 +59,8 @@ inline std::string type_string(const char* cls, const GemmArgument* a)
 template <typename ALayout, typename BLayout, typename CLayout, typename ADataType, typename BDataType,
           typename ScaleDataType, typename CDataType, typename AccDataType, typename CShuffleDataType,
           typename AElementwiseOperation, typename BElementwiseOperation, typename CElementwiseOperation,
-          GemmSpecialization GemmSpec = GemmSpecialization::Default, typename... Unused>
-struct DeviceFpAintBGemm_Wmma_CShuffle
+          GemmSpecialization GemmSpec = GemmSpecialization::Default>
+struct DeviceFpAintBGemm_Sm100
     : public DeviceGemm_dequantB<ALayout, BLayout, CLayout, ADataType, BDataType, CDataType, AElementwiseOperation,
                                  BElementwiseOperation, CElementwiseOperation>
 {
@@ -73,7 +85,7 @@ struct DeviceFpAintBGemm_Wmma_CShuffle
     }
     static Invoker MakeInvoker() { return Invoker{}; }
     static bool IsSupportedArgument(const Argument& arg) { return arg.plan.supported != 0; }
-    bool IsSupportedArgument(const BaseArgument* p) override { return IsSupportedArgument(*dynamic_cast<const Argument*>(p)); }
+    bool IsSupportedArgument(const BaseArgument* p) override { return IsSupportedArgument(ckb_detail::checked(p)); }
 
     std::unique_ptr<BaseArgument> MakeArgumentPointer(const void* p_a, const void* p_b, const void* p_scale, void* p_c,
                                                       index_t M, index_t N, index_t K, index_t StrideA, index_t StrideB,
@@ -85,8 +97,15 @@ struct DeviceFpAintBGemm_Wmma_CShuffle
                                                        K, StrideA, StrideB, StrideC, a, b, c));
     }
     std::unique_ptr<BaseInvoker> MakeInvokerPointer() override { return std::make_unique<Invoker>(); }
-    size_t GetWorkSpaceSize(const BaseArgument*) const override { return 0; } // as in the reference: internal
-    std::string GetTypeString() const override { return ckb_detail::type_string("DeviceFpAintBGemm_Wmma_CShuffle", nullptr); }
+    // honest workspace reporting (the reference ops on this path report 0 and need none): stream-K partial sums for decode-shaped
+    // problems, plus the K-major copy of a row-major int8 B.  A client that ignores it still runs (the argument then owns the bytes).
+    size_t GetWorkSpaceSize(const BaseArgument* p) const override { return ckb_detail::workspace_size(p); }
+    void SetWorkSpacePointer(BaseArgument* p, void* ws, const StreamConfig& sc = StreamConfig{}) const override
+    {
+        ckb_detail::set_workspace(p, ws, sc);
+    }
+    virtual const char* ClassName() const { return "DeviceFpAintBGemm_Sm100"; }
+    std::string GetTypeString() const override { return ckb_detail::type_string(ClassName()); }
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -94,8 +113,8 @@ struct DeviceFpAintBGemm_Wmma_CShuffle
 template <typename AsLayout, typename BsLayout, typename DsLayout, typename ELayout, typename AsDataType,
           typename BsDataType, typename AccDataType, typename CShuffleDataType, typename DsDataType, typename EDataType,
           typename AElementwiseOperation, typename BElementwiseOperation, typename CDEElementwiseOperation,
-          GemmSpecialization GemmSpec = GemmSpecialization::Default, typename... Unused>
-struct DeviceGemmMultipleABD_Xdl_CShuffle
+          GemmSpecialization GemmSpec = GemmSpecialization::Default>
+struct DeviceGemmMultipleABD_Sm100
     : public DeviceGemmMultipleABD<AsLayout, BsLayout, DsLayout, ELayout, AsDataType, BsDataType, DsDataType, EDataType,
                                    AElementwiseOperation, BElementwiseOperation, CDEElementwiseOperation>
 {
@@ -138,21 +157,13 @@ struct DeviceGemmMultipleABD_Xdl_CShuffle
         p.act = ckb_detail::cde_act_of<CDEElementwiseOperation>();
         p.e_dtype = ckb_detail::dtype_of<EDataType>(); p.e = p_e; p.lde = StrideE;
         if(p.b_layout == CKB_ROW && p.b_dtype == CKB_I8 && arg.why.empty())
-        {
-            // mk_kn_mn (client_example/30 default): the kernels stream K-major weights, so the argument keeps a
-            // one-time transposed copy of the static weight (a pre-pack, like UnsignedWeightPreprocessor)
-            void* t = nullptr;
-            ckb_detail::cuda_check(cudaMalloc(&t, size_t(N) * K), "cudaMalloc(B transposed)");
-            arg.own_b = std::shared_ptr<void>(t, [](void* q) { cudaFree(q); });
-            if(ckb_prepack_b_rowmajor_i8(p.b, p.ldb, K, N, t, nullptr) != CKB_OK) arg.why = ckb_last_error();
-            p.b = t; p.ldb = K; p.b_layout = CKB_COL;
-        }
+            arg.DeferRowMajorB(); // mk_kn_mn: no allocation and no launch here (see GemmArgument::DeferRowMajorB)
         if(arg.why.empty()) arg.Query();
         return arg;
     }
     static Invoker MakeInvoker() { return Invoker{}; }
     static bool IsSupportedArgument(const Argument& arg) { return arg.plan.supported != 0; }
-    bool IsSupportedArgument(const BaseArgument* p) override { return IsSupportedArgument(*dynamic_cast<const Argument*>(p)); }
+    bool IsSupportedArgument(const BaseArgument* p) override { return IsSupportedArgument(ckb_detail::checked(p)); }
     std::unique_ptr<BaseArgument>
     MakeArgumentPointer(std::array<const void*, NumATensor> p_as, std::array<const void*, NumBTensor> p_bs,
                         std::array<const void*, NumDTensor> p_ds, void* p_e, index_t M, index_t N, index_t K,
@@ -163,7 +174,15 @@ struct DeviceGemmMultipleABD_Xdl_CShuffle
         return std::make_unique<Argument>(MakeArgument(p_as, p_bs, p_ds, p_e, M, N, K, StrideAs, StrideBs, StrideDs, StrideE, a, b, c));
     }
     std::unique_ptr<BaseInvoker> MakeInvokerPointer() override { return std::make_unique<Invoker>(); }
-    std::string GetTypeString() const override { return ckb_detail::type_string("DeviceGemmMultipleABD_Xdl_CShuffle", nullptr); }
+    // honest workspace reporting (the reference ops on this path report 0 and need none): stream-K partial sums for decode-shaped
+    // problems, plus the K-major copy of a row-major int8 B.  A client that ignores it still runs (the argument then owns the bytes).
+    size_t GetWorkSpaceSize(const BaseArgument* p) const override { return ckb_detail::workspace_size(p); }
+    void SetWorkSpacePointer(BaseArgument* p, void* ws, const StreamConfig& sc = StreamConfig{}) const override
+    {
+        ckb_detail::set_workspace(p, ws, sc);
+    }
+    virtual const char* ClassName() const { return "DeviceGemmMultipleABD_Sm100"; }
+    std::string GetTypeString() const override { return ckb_detail::type_string(ClassName()); }
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -171,8 +190,8 @@ struct DeviceGemmMultipleABD_Xdl_CShuffle
 template <typename ALayout, typename BLayout, typename DsLayout, typename ELayout, typename ADataType, typename BDataType,
           typename AccDataType, typename CShuffleDataType, typename DsDataType, typename EDataType,
           typename AElementwiseOperation, typename BElementwiseOperation, typename CDEElementwiseOperation,
-          GemmSpecialization GemmSpec = GemmSpecialization::Default, typename... Unused>
-struct DeviceGemmMultipleD_Xdl_CShuffle
+          GemmSpecialization GemmSpec = GemmSpecialization::Default>
+struct DeviceGemmMultipleD_Sm100
     : public DeviceGemmMultipleD<ALayout, BLayout, DsLayout, ELayout, ADataType, BDataType, DsDataType, EDataType,
                                  AElementwiseOperation, BElementwiseOperation, CDEElementwiseOperation>
 {
@@ -203,7 +222,7 @@ struct DeviceGemmMultipleD_Xdl_CShuffle
     }
     static Invoker MakeInvoker() { return Invoker{}; }
     static bool IsSupportedArgument(const Argument& arg) { return arg.plan.supported != 0; }
-    bool IsSupportedArgument(const BaseArgument* p) override { return IsSupportedArgument(*dynamic_cast<const Argument*>(p)); }
+    bool IsSupportedArgument(const BaseArgument* p) override { return IsSupportedArgument(ckb_detail::checked(p)); }
     std::unique_ptr<BaseArgument> MakeArgumentPointer(const void* p_a, const void* p_b, std::array<const void*, NumDTensor> p_ds,
                                                       void* p_e, index_t M, index_t N, index_t K, index_t StrideA,
                                                       index_t StrideB, std::array<index_t, NumDTensor> StrideDs,
@@ -213,11 +232,17 @@ struct DeviceGemmMultipleD_Xdl_CShuffle
         return std::make_unique<Argument>(MakeArgument(p_a, p_b, p_ds, p_e, M, N, K, StrideA, StrideB, StrideDs, StrideE, a, b, c));
     }
     std::unique_ptr<BaseInvoker> MakeInvokerPointer() override { return std::make_unique<Invoker>(); }
-    std::string GetTypeString() const override { return ckb_detail::type_string("DeviceGemmMultipleD_Xdl_CShuffle", nullptr); }
+    // honest workspace reporting (the reference ops on this path report 0 and need none): stream-K partial sums for decode-shaped
+    // problems, plus the K-major copy of a row-major int8 B.  A client that ignores it still runs (the argument then owns the bytes).
+    size_t GetWorkSpaceSize(const BaseArgument* p) const override { return ckb_detail::workspace_size(p); }
+    void SetWorkSpacePointer(BaseArgument* p, void* ws, const StreamConfig& sc = StreamConfig{}) const override
+    {
+        ckb_detail::set_workspace(p, ws, sc);
+    }
+    virtual const char* ClassName() const { return "DeviceGemmMultipleD_Sm100"; }
+    std::string GetTypeString() const override { return ckb_detail::type_string(ClassName()); }
 };
 
-template <typename... Ts>
-using DeviceGemmMultiD_Xdl_CShuffle_V3 = DeviceGemmMultipleD_Xdl_CShuffle<Ts...>;
 
 // ------------------------------------------------------------------------------------------------
 // [EXT] W4A16 with K-blocked scales / zero points on pre-packed int4 weights
@@ -247,7 +272,7 @@ struct DeviceGemm_dequantB_GroupScale_Sm100
     }
     static Invoker MakeInvoker() { return Invoker{}; }
     static bool IsSupportedArgument(const Argument& arg) { return arg.plan.supported != 0; }
-    bool IsSupportedArgument(const BaseArgument* p) override { return IsSupportedArgument(*dynamic_cast<const Argument*>(p)); }
+    bool IsSupportedArgument(const BaseArgument* p) override { return IsSupportedArgument(ckb_detail::checked(p)); }
     std::unique_ptr<BaseArgument> MakeArgumentPointer(const void* p_a, const void* p_b, const void* p_scale, const void* p_zero,
                                                       void* p_c, index_t M, index_t N, index_t K, index_t StrideA, index_t StrideC,
                                                       index_t zp, AElementwiseOperation a, BElementwiseOperation b,
@@ -261,7 +286,7 @@ struct DeviceGemm_dequantB_GroupScale_Sm100
     {
         ckb_detail::set_workspace(p, ws, sc);
     }
-    std::string GetTypeString() const override { return ckb_detail::type_string("DeviceGemm_dequantB_GroupScale_Sm100", nullptr); }
+    std::string GetTypeString() const override { return ckb_detail::type_string("DeviceGemm_dequantB_GroupScale_Sm100"); }
 };
 
 } // namespace device

@@ -45,20 +45,13 @@ struct DeviceGemm_Xdl_CShuffleV3R1
         p.kbatch  = KSplit;
         if(KSplit < 1) arg.why = "KSplit must be >= 1";
         if(p.b_layout == CKB_ROW && p.b_dtype == CKB_I8 && arg.why.empty())
-        {
-            // mk_kn_mn: the kernels stream K-major weights; keep a one-time transposed copy of the static weight
-            void* t = nullptr;
-            ckb_detail::cuda_check(cudaMalloc(&t, size_t(N) * K), "cudaMalloc(B transposed)");
-            arg.own_b = std::shared_ptr<void>(t, [](void* q) { cudaFree(q); });
-            if(ckb_prepack_b_rowmajor_i8(p.b, p.ldb, K, N, t, nullptr) != CKB_OK) arg.why = ckb_last_error();
-            p.b = t; p.ldb = K; p.b_layout = CKB_COL;
-        }
+            arg.DeferRowMajorB(); // mk_kn_mn: no allocation and no launch here (see GemmArgument::DeferRowMajorB)
         if(arg.why.empty()) arg.Query();
         return arg;
     }
     static Invoker MakeInvoker() { return Invoker{}; }
     static bool IsSupportedArgument(const Argument& arg) { return arg.plan.supported != 0; }
-    bool IsSupportedArgument(const BaseArgument* p) override { return IsSupportedArgument(*dynamic_cast<const Argument*>(p)); }
+    bool IsSupportedArgument(const BaseArgument* p) override { return IsSupportedArgument(ckb_detail::checked(p)); }
     std::unique_ptr<BaseArgument>
     MakeArgumentPointer(const void* p_a, const void* p_b, std::array<const void*, NumDTensor> p_ds, void* p_c, index_t M, index_t N, index_t K,
                         index_t StrideA, index_t StrideB, std::array<index_t, NumDTensor> StrideDs, index_t StrideC, index_t KSplit,
@@ -72,7 +65,7 @@ struct DeviceGemm_Xdl_CShuffleV3R1
     {
         ckb_detail::set_workspace(p, ws, sc);
     }
-    std::string GetTypeString() const override { return ckb_detail::type_string("DeviceGemm_Xdl_CShuffleV3R1", nullptr); }
+    std::string GetTypeString() const override { return ckb_detail::type_string("DeviceGemm_Xdl_CShuffleV3R1"); }
 };
 
 } // namespace device

@@ -95,4 +95,5 @@ enum struct BlockGemmPipelineScheduler { Intrawave, Interwave };
 enum struct BlockGemmPipelineVersion { v1, v2, v3, v4, v5 };
 enum struct PipelineVersion { v1, v2, v4, weight_only };
 enum struct LoopScheduler { Default, Interwave };
+constexpr LoopScheduler make_default_loop_scheduler() { return LoopScheduler::Default; } // gridwise_gemm_pipeline_selector.hpp
 } // namespace ck

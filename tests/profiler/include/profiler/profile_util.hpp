@@ -3,6 +3,7 @@
 // run once and verify against the host reference -> time -> "Perf:" line -> keep the best) plus the B200 roofline
 // columns (fraction of the measured HBM copy bandwidth and of the dense tensor peak).
 #pragma once
+#include <algorithm>
 #include <cstdlib>
 #include <functional>
 #include <iomanip>
@@ -25,6 +26,24 @@ struct Peaks
     }
 };
 
+// Cold-cache timing options (the reference's "memory for rotating buffer" argument of profile_gemm_multiply_multiply.cpp:31 and
+// profile_gemm_universal*.cpp): rotating_mb > 0 -> StreamConfig::flush_cache with enough rotating A/B copies to cover that many
+// MB, L2 evicted before every timed launch, median of the launches (include/ck/host_utility/flush_cache.hpp).
+// Set from an op's own argument or, for every op, from CKP_ROTATING_MB.
+struct Options
+{
+    int rotating_mb = 0;
+    Options()
+    {
+        if(const char* e = std::getenv("CKP_ROTATING_MB")) rotating_mb = std::atoi(e);
+    }
+};
+inline Options& options()
+{
+    static Options o;
+    return o;
+}
+
 struct Best
 {
     std::string name;
@@ -40,6 +59,11 @@ inline void print_perf(const char* tag, float ms, double flop, double bytes, con
     std::cout << tag << std::setw(10) << ms << " ms, " << tflops << " TFlops, " << gbs << " GB/s, " << name << "  [roofline: "
               << std::fixed << std::setprecision(1) << 100.0 * gbs / pk.hbm_gbs << "% HBM, "
               << 100.0 * tflops / (pk.tensor_tfs * tensor_scale) << "% tensor]" << std::defaultfloat << std::setprecision(6) << std::endl;
+    // one machine-readable line per result (metrics / logging row)
+    std::cout << "PerfJSON: {\"tag\": \"" << (best ? "perf" : "best") << "\", \"instance\": \"" << name << "\", \"ms\": " << ms << ", \"tflops\": " << tflops
+              << ", \"gbs\": " << gbs << ", \"hbm_frac\": " << gbs / pk.hbm_gbs << ", \"tensor_frac\": " << tflops / (pk.tensor_tfs * tensor_scale)
+              << ", \"rotating_mb\": " << options().rotating_mb << ", \"timing\": \"" << (options().rotating_mb > 0 ? "cold: rotating buffers + L2 flush, median" : "warm: back-to-back launches, mean")
+              << "\"}" << std::endl;
     if(best && tflops > best->tflops) { best->tflops = tflops; best->gbs = gbs; best->ms = ms; best->name = name; }
 }
 
@@ -68,7 +92,13 @@ bool run_instances(OpPtrs& op_ptrs, MakeArg make_arg, Prepare prepare, Verify ve
         if(do_verification) best.pass = verify() && best.pass;
         if(time_kernel)
         {
-            const float ms = invoker_ptr->Run(argument_ptr.get(), StreamConfig{nullptr, true, 0, n_warmup, n_iter});
+            StreamConfig sc{nullptr, true, 0, n_warmup, n_iter};
+            if(options().rotating_mb > 0)
+            {
+                sc.flush_cache    = true;
+                sc.rotating_count = std::max(2, int((double(options().rotating_mb) * 1.0e6 + bytes - 1) / bytes));
+            }
+            const float ms = invoker_ptr->Run(argument_ptr.get(), sc);
             print_perf("Perf: ", ms, flop, bytes, op_ptr->GetTypeString(), tensor_scale, &best);
         }
     }

@@ -11,6 +11,7 @@
 #include "ck/library/utility/device_memory.hpp"
 #include "ck/library/utility/fill.hpp"
 #include "ck/library/utility/host_tensor.hpp"
+#include "ck/tensor_operation/gpu/device/impl/device_fpAintB_gemm_wmma.hpp"
 #include "ck/tensor_operation/gpu/device/impl/device_gemm_sm100.hpp"
 #include "profiler/profile_util.hpp"
 #include "profiler_operation_registry.hpp"

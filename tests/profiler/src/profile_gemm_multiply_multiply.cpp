@@ -28,7 +28,7 @@ int profile_gemm_multiply_multiply(int argc, char* argv[])
         printf("arg7: time kernel (0=no, 1=yes)\n");
         printf("arg8 to 15: M, N, K, StrideA, StrideB, StrideD0, StrideD1, StrideE\n");
         printf("optional:\narg16: number of warm-up cycles (default 1)\narg17: number of iterations (default 10)\n");
-        printf("arg18: memory for rotating buffer (accepted, unused)\n");
+        printf("arg18: memory for rotating buffer (MB; > 0: cold-cache timing with rotating A/B copies and an L2 flush before each launch)\n");
         return 1;
     }
     const int data_type = std::stoi(argv[2]), layout = std::stoi(argv[3]);
@@ -41,7 +41,7 @@ int profile_gemm_multiply_multiply(int argc, char* argv[])
     const int StrideD0 = std::max(0, std::stoi(argv[13])), StrideD1 = std::max(0, std::stoi(argv[14]));
     const int StrideE = dflt(std::stoi(argv[15]), N);
     int n_warmup = 1, n_iter = 10;
-    if(argc == 19) { n_warmup = std::stoi(argv[16]); n_iter = std::stoi(argv[17]); }
+    if(argc == 19) { n_warmup = std::stoi(argv[16]); n_iter = std::stoi(argv[17]); ck::profiler::options().rotating_mb = std::stoi(argv[18]); }
     if(data_type != 3 || layout != 1)
     {
         std::cout << "this data_type & layout is not implemented" << std::endl;

@@ -154,3 +154,17 @@ def test_grouped_argument_layout_and_query_without_gpu():
     assert lib.ckb_grouped_gemm_query(C.byref(p), 16) == capi.ERR_UNSUPPORTED   # km_kn_mn is not built
     p.a_layout, p.num_d = capi.ROW, 0
     assert lib.ckb_grouped_gemm_query(C.byref(p), 16) == capi.ERR_UNSUPPORTED   # AddFastGelu needs its D tensor
+
+
+def test_reference_instance_declarations_compile_and_construct():
+    """tests/cpp/verbatim_instances.cpp holds the reference's own instance declarations (full template argument lists of
+    examples 64 / 14 / 60 and the V3 order of example 65); built by __graft_entry__.build(), it must construct the four
+    operators without a GPU and report the reference class names."""
+    import subprocess
+    exe = os.path.join(os.path.dirname(os.path.abspath(__file__)), "cpp", "bin", "verbatim_instances")
+    if not os.path.exists(exe):
+        pytest.skip("tests/cpp not built")
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0, r.stderr[-1000:]
+    for cls in ("DeviceFpAintBGemm_Wmma_CShuffle", "DeviceGemmMultipleD_Xdl_CShuffle", "DeviceGemmMultipleABD_Xdl_CShuffle", "DeviceGemmMultiD_Xdl_CShuffle_V3"):
+        assert cls + "<sm_100a" in r.stdout

@@ -25,6 +25,10 @@ CASES = [
     ("client_grouped_gemm_fastgelu_bf16_i8", ["0"]),                             # client 31 FastGelu: KernelArgument<1,2,0> (NumD = 0)
     ("client_grouped_gemm_fastgelu_bf16_i8", ["1"]),                             # client 31 plain: PassThrough, NumD = 0
     ("client_grouped_gemm_fastgelu_bf16_i8", ["0", "5", "256", "192", "1"]),     # NumD = 0, mk_nk_mn
+    ("example_w4a16_group_gemm", ["16", "512", "1024", "1", "0", "1"]),          # DequantizeGroupRound contract, decode rows
+    ("example_w4a16_group_gemm", ["200", "512", "1024", "0", "0", "1"]),         # DequantizeGroupRound, prefill rows (tcgen05)
+    ("example_w4a16_group_gemm", ["200", "512", "1024", "1", "0", "0"]),         # DequantizeGroup above 64 rows (row slabs)
+    ("interfaces_plain", []),                                                    # DeviceGemm / SplitK / StreamK / V3 / ABScale
 ]
 
 PROFILER = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiler", "bin", "ckProfiler")
@@ -65,6 +69,34 @@ def test_ck_profiler(args):
     assert "verification PASSED" in r.stdout
     if args[0] != "gemm_multi_abd" or args[7] == "1":
         assert "Best Perf:" in r.stdout
+
+
+def test_verbatim_reference_instances_run():
+    """the reference's own instance declarations (full template argument lists) compile against include/ck and run"""
+    r = subprocess.run([os.path.join(BIN, "verbatim_instances"), "run"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-2000:])
+    for cls in ("DeviceFpAintBGemm_Wmma_CShuffle<sm_100a", "DeviceGemmMultipleD_Xdl_CShuffle<sm_100a", "DeviceGemmMultipleABD_Xdl_CShuffle<sm_100a",
+                "DeviceGemmMultiD_Xdl_CShuffle_V3<sm_100a"):
+        assert cls in r.stdout
+    assert "gemm_ss" in r.stdout          # GetTypeString names the chosen kernel once an argument has been made
+
+
+def test_ck_profiler_rotating_buffers_report_the_hbm_number():
+    """with rotating buffers + L2 flush (flush_cache.hpp semantics) a decode-shaped GEMM whose weights fit the
+    126 MB L2 must time SLOWER than the warm back-to-back loop, i.e. the profiler reports the HBM number, not the L2 number."""
+    import json
+    args = ["gemm_w4a16", "0", "2", "0", "1", "1", "11008", "4096", "0", "3", "30"]
+
+    def perf(env):
+        r = subprocess.run([PROFILER] + args, capture_output=True, text=True, timeout=300, env={**os.environ, **env})
+        assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-2000:])
+        rows = [json.loads(l.split("PerfJSON: ", 1)[1]) for l in r.stdout.splitlines() if l.startswith("PerfJSON: ")]
+        assert rows and all(k in rows[0] for k in ("instance", "ms", "gbs", "hbm_frac", "timing"))
+        return rows[0]
+    warm = perf({"CKP_ROTATING_MB": "0"})
+    cold = perf({"CKP_ROTATING_MB": "512"})
+    assert "warm" in warm["timing"] and "cold" in cold["timing"]
+    assert cold["ms"] > 1.1 * warm["ms"], (warm, cold)
 
 
 def test_ck_profiler_unknown_operation_and_help():
