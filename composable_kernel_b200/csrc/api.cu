@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "kernels.h"
+#include "tile_map.cuh"
 
 namespace ckb {
 namespace {
@@ -89,6 +90,37 @@ extern "C" {
 const char* ckb_last_error(void) { return last_error().c_str(); }
 int ckb_version(void) { return CKB_VERSION; }
 int ckb_device_sm_count(void) { return device_info().ok ? device_info().sm_count : -1; }
+
+int ckb_tile_coord(int32_t t, int32_t num_m_blk, int32_t num_n_blk, int32_t group, int32_t* mb, int32_t* nb)
+{
+    if(!mb || !nb || num_m_blk <= 0 || num_n_blk <= 0 || group <= 0 || t < 0 || t >= num_m_blk * num_n_blk)
+        return set_error(CKB_ERR_INVALID, "ckb_tile_coord: bad argument");
+    int m = 0, n = 0;
+    tile_coord(t, num_m_blk, num_n_blk, m, n, group);
+    *mb = m; *nb = n;
+    return CKB_OK;
+}
+
+int ckb_streamk_range(int64_t total_units, int32_t cta, int32_t grid, int64_t* begin, int64_t* end)
+{
+    if(!begin || !end || grid <= 0 || cta < 0 || cta >= grid || total_units < 0) return set_error(CKB_ERR_INVALID, "ckb_streamk_range: bad argument");
+    long long b = 0, e = 0;
+    streamk_range(total_units, cta, grid, b, e);
+    *begin = b; *end = e;
+    return CKB_OK;
+}
+
+int ckb_gemv_schedule(int32_t M, int32_t N, int32_t K, int32_t zero_points, int32_t sms, int32_t mode, int32_t* out)
+{
+    if(!out || N <= 0 || K <= 0 || sms <= 0) return set_error(CKB_ERR_INVALID, "ckb_gemv_schedule: bad argument");
+    G2Sched s{};
+    if(int rc = schedule_wq_gemv2(M, N, K, zero_points != 0, sms, s, mode)) return rc;
+    const int32_t v[24] = {s.nt, s.rb, s.n_groups, s.kb_total, s.grid, s.passes, s.n_slots, s.slot_q, s.slot_r, s.g_hi, s.wn_log2, s.gw,
+                           s.kbu, s.upw, s.n_chunks, s.ring, s.stage_bytes, s.off_w, s.off_s, s.off_z, s.red_off, s.bar_off, s.smem_bytes,
+                           s.nt == 1 ? 16 : 8};
+    for(int i = 0; i < 24; ++i) out[i] = v[i];
+    return CKB_OK;
+}
 
 int ckb_peer_wait(void* flag, void* epoch_state, uint32_t arrivals_per_epoch, void* stream)
 {

@@ -24,4 +24,12 @@ CKB_HD void tile_coord(int t, int num_m_blk, int num_n_blk, int& mb, int& nb, in
     nb                  = r / rows;
 }
 
+// stream-K: CTA `cta` of `grid` owns the contiguous range [begin, end) of the flattened (n-tile, k-unit) space -- equal shares,
+// the remainder spread over the CTAs (the role of BlockToCTileMap_GemmStreamK, grid/block_to_ctile_map.hpp:1016-1400)
+CKB_HD void streamk_range(long long total_units, int cta, int grid, long long& begin, long long& end)
+{
+    begin = total_units * cta / grid;
+    end   = total_units * (cta + 1) / grid;
+}
+
 } // namespace ckb

@@ -29,6 +29,7 @@
 #include "epilogue.cuh"
 #include "kernels.h"
 #include "ptx.cuh"
+#include "tile_map.cuh"
 
 #include <vector>
 
@@ -275,8 +276,8 @@ wq_decode_kernel(const __grid_constant__ CUtensorMap tmAct, const __grid_constan
     if(threadIdx.x == 0) CKB_TR(5, 0, 1);
     if(threadIdx.x == 0) CKB_GT(1);
 
-    const long long u_begin = args.total_units * blockIdx.x / gridDim.x;
-    const long long u_end   = args.total_units * (blockIdx.x + 1) / gridDim.x;
+    long long u_begin, u_end;
+    streamk_range(args.total_units, int(blockIdx.x), int(gridDim.x), u_begin, u_end);
     const int n_my          = int(u_end - u_begin);
     const int k_units       = args.k_units;
     const int nt0           = int(u_begin / k_units); // first tile / k-unit of this CTA (one division)

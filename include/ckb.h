@@ -244,6 +244,17 @@ int ckb_grouped_gemm_run(const ckb_gemm_problem* proto, const void* dev_args, in
    Graph-capturable (all state lives in device memory). */
 int ckb_peer_wait(void* flag, void* epoch_state, uint32_t arrivals_per_epoch, void* stream);
 
+/* ---- scheduler arithmetic, host only (no device needed): the functions the kernels themselves use, exported so that the
+        tile maps are unit-tested on the CPU in the style of the reference's test/block_to_ctile_map ------------------------- */
+/* output-tile raster of the persistent tcgen05 kernels: linear tile index t -> (m block, n block), bands of `group` M blocks */
+int ckb_tile_coord(int32_t t, int32_t num_m_blk, int32_t num_n_blk, int32_t group, int32_t* mb, int32_t* nb);
+/* stream-K unit range [begin, end) of CTA `cta` out of `grid` */
+int ckb_streamk_range(int64_t total_units, int32_t cta, int32_t grid, int64_t* begin, int64_t* end);
+/* W4A16 decode kernel schedule for (M, N, K) on `sms` SMs; mode bit 0 = CKB_FLAG_FIXED_K_ORDER, bit 1 = GROUP_RTN.  out[24] =
+   {nt, rb, n_groups, kb_total, grid, passes, n_slots, slot_q, slot_r, g_hi, wn_log2, gw, kbu, upw, n_chunks, ring, stage_bytes,
+    off_w, off_s, off_z, red_off, bar_off, smem_bytes, warps}.  Returns CKB_ERR_UNSUPPORTED when no schedule fits. */
+int ckb_gemv_schedule(int32_t M, int32_t N, int32_t K, int32_t zero_points, int32_t sms, int32_t mode, int32_t* out);
+
 /* ---- misc --------------------------------------------------------------------------------- */
 const char* ckb_last_error(void);
 int ckb_version(void);

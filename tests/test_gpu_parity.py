@@ -382,3 +382,67 @@ def test_grouped_unsupported_and_null_args():
     # Run without SetDeviceKernelArgs: the reference throws (device_grouped_gemm_multi_abd_xdl_fixed_nk.hpp:597-600)
     rc = capi.lib().ckb_grouped_gemm_run(C.byref(op.problem), None, 1, 4, None)
     assert rc == capi.ERR_INVALID
+
+
+# ------------------------------------------------------------------------------------------ layout tool, converter identities
+@pytest.mark.parametrize("K,N", [(64, 16), (192, 100), (4096, 512)])
+def test_device_prepack_equals_host_packer(K, N):
+    """ckb_prepack_b_int4 (device) and composable_kernel_b200.packing.pack_int4 (numpy, offline tool) write the same bytes"""
+    import torch
+    from composable_kernel_b200 import ops, packing
+    rng = np.random.default_rng(K * N)
+    q = rng.integers(0, 16, (K, N), dtype=np.uint8)
+    dev = ops.prepack_int4(H.to_dev(q)).cpu().numpy()
+    host = packing.pack_int4(q).reshape(-1).view(np.uint8)
+    assert dev.size == host.size and np.array_equal(dev, host)
+
+
+def test_gptq_checkpoint_import_runs_through_the_gemm():
+    """AutoGPTQ qweight [K/8, N] int32 -> codes -> host packer -> device GEMM == oracle on the same codes"""
+    import torch
+    from composable_kernel_b200 import capi, ops, packing
+    o = orc()
+    rng = np.random.default_rng(8)
+    M, N, K = 4, 256, 512
+    q = rng.integers(0, 16, (K, N), dtype=np.uint8)
+    qweight = np.zeros((K // 8, N), np.uint32)
+    for i in range(8):
+        qweight |= q[i::8].astype(np.uint32) << np.uint32(4 * i)
+    packed = packing.pack_int4(packing.codes_from_gptq(qweight.view(np.int32)))
+    a = rand_bf16(rng, (M, K))
+    s = o.bf16_trunc((rng.random((K // 128, N)) * 0.015 + 0.005).astype(np.float32))
+    e = torch.zeros(M, N, dtype=torch.float32, device="cuda")
+    op = ops.GemmOp(H.to_dev(a, True), torch.from_numpy(packed.reshape(-1).view(np.uint8)).cuda(), e, b_dtype=capi.I4, b_layout=capi.PREPACKED,
+                    b_op=capi.BOP_GROUP, N=N, K=K, scale=H.to_dev(s, True), zero_const=8, group_size=128)
+    assert op.supported, op.why
+    op.run()
+    torch.cuda.synchronize()
+    ref = o.gemm(a, o.BF16, q, o.U8, o.F32, b_op=o.BOP_GROUP_F32, scale=s, s_dtype=o.BF16, zero_const=8, group_size=128)
+    bad, err = H.f_close(e.cpu().numpy(), ref, 1e-4, 1e-3)
+    assert bad == 0, err
+
+
+@pytest.mark.parametrize("M", [1, 128])
+def test_device_int8_converters_all_256_codes(M):
+    """Reference-held identities on the DEVICE kernels (decode and prefill variants): with a one-hot activation row the GEMM
+    returns the dequantised weight itself, so every int8 code must come back as fp16(q) * s (fpAintB: the 0x6400|u8 - 0x6480
+    converter, unary_element_wise_operation.hpp:1061-1091) and as trunc_bf16(float(q) * float(s)) (Multiply<bhalf_t,int8_t,bhalf_t>,
+    binary_element_wise_operation.hpp:184-190) -- bit exact, all 256 codes against a grid of scales."""
+    o = orc()
+    K, N = 128, 2560
+    qs = np.arange(-128, 128, dtype=np.int32)
+    code = np.tile(qs, N // 256).astype(np.int8)                      # column n carries code n % 256
+    scales_f = np.array([1.0, 0.5, 0.0078125, 0.013, 0.0999, 1.7, 3.14159, 1e-3, 2.0, 0.25], np.float32)
+    s_col = np.repeat(scales_f, 256)                                  # column block j uses scale j
+    qn = np.zeros((N, K), np.int8)
+    qn[:, 3] = code                                                   # only k = 3 is populated
+    a16 = np.zeros((M, K), np.float16); a16[:, 3] = 1.0
+    got, op = H.run_fpaintb(a16, qn, s_col.astype(np.float16))
+    want = (code.astype(np.float16) * s_col.astype(np.float16))       # one fp16 rounding of q * s (reference_fpAintB_gemm.hpp:110)
+    assert np.array_equal(got[0].view(np.uint16), want.view(np.uint16)), op.kernel_name
+    abf = np.zeros((M, K), np.float32); abf[:, 3] = 1.0
+    sb = o.bf16_trunc(s_col)
+    gotb, opb = H.run_w8a16_bf16(o.bf16_trunc(abf), qn, sb, np.zeros(N, np.uint16), "pass")
+    prod = code.astype(np.float32) * o.bf16_to_f32(sb)
+    wantb = (prod.view(np.uint32) >> 16).astype(np.uint16)
+    assert np.array_equal(gotb[0], wantb), opb.kernel_name
