@@ -1,3 +1,6 @@
+// SPDX-License-Identifier: MIT
+// Interface mirrored from Composable Kernel (Copyright (c) Advanced Micro Devices, Inc., MIT licence): declarations must match the
+// reference for client code to compile unchanged; see the reference file cited below.
 // ck/tensor_operation/gpu/device/device_base.hpp -- BaseArgument / BaseInvoker / BaseOperator with the
 // reference's exact surface (include/ck/tensor_operation/gpu/device/device_base.hpp:15-71).
 #pragma once

@@ -1,3 +1,6 @@
+// SPDX-License-Identifier: MIT
+// Interface mirrored from Composable Kernel (Copyright (c) Advanced Micro Devices, Inc., MIT licence): declarations must match the
+// reference for client code to compile unchanged; see the reference file cited below.
 // DeviceGemm_dequantB interface (include/ck/tensor_operation/gpu/device/device_gemm_dequantB.hpp:24-42)
 #pragma once
 #include <memory>

@@ -1,3 +1,6 @@
+// SPDX-License-Identifier: MIT
+// Interface mirrored from Composable Kernel (Copyright (c) Advanced Micro Devices, Inc., MIT licence): declarations must match the
+// reference for client code to compile unchanged; see the reference file cited below.
 // DeviceGemmMultipleD interface (include/ck/tensor_operation/gpu/device/device_gemm_multiple_d.hpp:33-54)
 #pragma once
 #include <array>

@@ -1,3 +1,6 @@
+// SPDX-License-Identifier: MIT
+// Interface mirrored from Composable Kernel (Copyright (c) Advanced Micro Devices, Inc., MIT licence): declarations must match the
+// reference for client code to compile unchanged; see the reference file cited below.
 // DeviceGemmV2 / DeviceGemmV2R1 interfaces (include/ck/tensor_operation/gpu/device/device_gemm_v2.hpp:14-74): plain GEMM with a
 // split-K argument (KBatch / KSplit); V2R1 adds D tensors applied by the reduction step.
 #pragma once

@@ -1,3 +1,6 @@
+// SPDX-License-Identifier: MIT
+// Interface mirrored from Composable Kernel (Copyright (c) Advanced Micro Devices, Inc., MIT licence): declarations must match the
+// reference for client code to compile unchanged; see the reference file cited below.
 // DeviceGroupedGemmMultiABD / GemmMultiABDDesc -- same surface as the reference's
 // include/ck/tensor_operation/gpu/device/device_grouped_gemm_multi_abd.hpp:14-94.
 #pragma once

@@ -1,3 +1,6 @@
+// SPDX-License-Identifier: MIT
+// Interface mirrored from Composable Kernel (Copyright (c) Advanced Micro Devices, Inc., MIT licence): declarations must match the
+// reference for client code to compile unchanged; see the reference file cited below.
 // GroupedGemmMultiABDKernelArgument / DeviceGroupedGemmMultiABDFixedNK -- same surface (and, for the argument
 // struct, the same memory layout: the kernel reads it from device memory) as the reference's
 // include/ck/tensor_operation/gpu/device/device_grouped_gemm_multi_abd_fixed_nk.hpp:15-77.

@@ -1,3 +1,6 @@
+// SPDX-License-Identifier: MIT
+// Interface mirrored from Composable Kernel (Copyright (c) Advanced Micro Devices, Inc., MIT licence): declarations must match the
+// reference for client code to compile unchanged; see the reference file cited below.
 // ckProfiler <operation> <args...> -- dispatches to the registered operation (profiler/src/profiler.cpp:14-30).
 #include <cstdlib>
 #include <iostream>

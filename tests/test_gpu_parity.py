@@ -446,3 +446,24 @@ def test_device_int8_converters_all_256_codes(M):
     prod = code.astype(np.float32) * o.bf16_to_f32(sb)
     wantb = (prod.view(np.uint32) >> 16).astype(np.uint16)
     assert np.array_equal(gotb[0], wantb), opb.kernel_name
+
+
+def test_torch_custom_ops_match_the_oracle():
+    import torch
+    from composable_kernel_b200 import ops, torch_ops  # noqa: F401
+    o = orc()
+    rng = np.random.default_rng(11)
+    M, N, K = 5, 512, 1024
+    a = rand_bf16(rng, (M, K))
+    q = rng.integers(0, 16, (K, N), dtype=np.uint8)
+    s = o.bf16_trunc((rng.random((K // 128, N)) * 0.015 + 0.005).astype(np.float32))
+    y = torch.ops.ckb.w4a16_linear(H.to_dev(a, True), ops.prepack_int4(H.to_dev(q)), H.to_dev(s, True), None, N, K, False)
+    ref = o.gemm(a, o.BF16, q, o.U8, o.BF16, b_op=o.BOP_GROUP_F32, scale=s, s_dtype=o.BF16, zero_const=8, group_size=128)
+    bad, err = H.bf16_close(H.from_dev_bf16(y), ref, RTOL, ATOL)
+    assert bad == 0, err
+    ai = rng.integers(-128, 128, (64, 256), dtype=np.int8); bn = rng.integers(-128, 128, (128, 256), dtype=np.int8)
+    d0 = (rng.random(128) * 1e-3).astype(np.float32); d1 = (rng.random(64) * 1e-3).astype(np.float32)
+    e = torch.ops.ckb.int8_gemm_scaled(H.to_dev(ai), H.to_dev(bn), H.to_dev(d0), H.to_dev(d1))
+    refe = o.gemm(ai, o.I8, bn.T, o.I8, o.BF16, cshuffle_dtype=o.I32, ds=(np.broadcast_to(d0, (64, 128)), np.broadcast_to(d1[:, None], (64, 128))),
+                  d_dtypes=(o.F32, o.F32), cde_op=o.CDE_MULTIPLY_MULTIPLY)
+    assert np.array_equal(H.from_dev_bf16(e), refe)

@@ -171,3 +171,22 @@ def test_multiply_bf16_int8_functor_all_codes_times_scale_grid():
     prod = q[0].astype(np.float32) * orc.bf16_to_f32(s[0])
     want = (prod.view(np.uint32) >> 16).astype(np.uint16)               # truncation = the upper 16 bits
     assert np.array_equal(e[0], want)
+
+
+# ------------------------------------------------------------------ torch custom ops: registration + fake (meta) shapes
+def test_torch_custom_ops_trace_with_fake_tensors():
+    import torch
+    from torch._subclasses.fake_tensor import FakeTensorMode
+    from composable_kernel_b200 import torch_ops  # noqa: F401  (registers torch.ops.ckb.*)
+    with FakeTensorMode():
+        x = torch.empty(2, 3, 4096, dtype=torch.bfloat16)
+        packed = torch.empty(packing.packed_bytes(11008, 4096), dtype=torch.uint8)
+        sc = torch.empty(32, 11008, dtype=torch.bfloat16)
+        y = torch.ops.ckb.w4a16_linear(x, packed, sc, None, 11008, 4096, False)
+        assert tuple(y.shape) == (2, 3, 11008) and y.dtype == torch.bfloat16
+        w = torch.empty(14336, 4096, dtype=torch.int8)
+        y8 = torch.ops.ckb.w8a16_linear(x, w, torch.empty(14336, dtype=torch.bfloat16), torch.empty(14336, dtype=torch.bfloat16))
+        assert tuple(y8.shape) == (2, 3, 14336)
+        a = torch.empty(64, 256, dtype=torch.int8)
+        e = torch.ops.ckb.int8_gemm_scaled(a, torch.empty(128, 256, dtype=torch.int8), torch.empty(128), torch.empty(64))
+        assert tuple(e.shape) == (64, 128) and e.dtype == torch.bfloat16
