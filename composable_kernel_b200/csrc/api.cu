@@ -231,11 +231,12 @@ int ckb_gemm_query(const ckb_gemm_problem* pp, ckb_gemm_plan* plan)
     // GROUP (fp32 group scale on partial sums) is always served by the HMMA decode kernels, in row slabs above 64 rows;
     // GROUP_RTN (one rounding into A's type) by the fused tcgen05 kernel above 64 rows and by the RTN instantiation of the
     // HMMA kernel below.
+    if((p.flags & CKB_FLAG_PREFILL_TWO_PASS) && p.M <= 64) return unsupported(plan, "the two-pass prefill instance serves M > 64");
     if(p.M > 64 && p.K % 8 == 0 && p.b_op != CKB_BOP_GROUP)
     {
         // prefill-shaped: the fused TMA -> dequant -> tcgen05 pair kernel (no workspace).  CKB_PREFILL_TWO_PASS=1 selects the
         // round-1 form (expand the weight into the workspace, then the dense GEMM) for comparison.
-        const bool two_pass = getenv("CKB_PREFILL_TWO_PASS") && atoi(getenv("CKB_PREFILL_TWO_PASS")) == 1;
+        const bool two_pass = (p.flags & CKB_FLAG_PREFILL_TWO_PASS) || (getenv("CKB_PREFILL_TWO_PASS") && atoi(getenv("CKB_PREFILL_TWO_PASS")) == 1);
         if(int rc = two_pass ? plan_wq_prefill(p, *plan) : plan_wq_fused(p, *plan)) return rc;
         plan->kernel_id = two_pass ? KID_WQ_PREFILL : KID_WQ_FUSED;
         plan->supported = 1;
@@ -247,7 +248,7 @@ int ckb_gemm_query(const ckb_gemm_problem* pp, ckb_gemm_plan* plan)
         // math (profiles/r2_gemv_variants.txt): the rotating-producer kernel (wq_gemv2, <= 32 rows per launch) wins where one
         // pass covers the CTA's channels and either M <= 8 or the whole K extent is resident in the ring; the single-producer
         // kernel (wq_gemv, <= 64 rows) wins on streaming shapes and on M > 8.  CKB_GEMV=1 / 2 forces one of them.
-        const int force = getenv("CKB_GEMV") ? atoi(getenv("CKB_GEMV")) : 0;
+        const int force = getenv("CKB_GEMV") ? atoi(getenv("CKB_GEMV")) : ((p.flags & CKB_FLAG_GEMV_SINGLE_PRODUCER) ? 1 : 0);
         // RTN numerics and the fixed-K-order contract exist in the rotating-producer kernel only
         const bool g2_only = p.b_op == CKB_BOP_GROUP_RTN || (p.flags & CKB_FLAG_FIXED_K_ORDER) || p.num_peers > 0;
         // rows beyond 32 go through 32-row slabs: the single-producer kernel's 64-row variant (8 token tiles) is retired -- its
@@ -444,6 +445,15 @@ int ckb_prepack_b_rowmajor_i8(const void* src, int64_t ld_src, int32_t K, int32_
     if(!src || !dst || K < 0 || N < 0 || ld_src < N) return set_error(CKB_ERR_INVALID, "bad prepack arguments");
     if(!device_info().ok) return set_error(CKB_ERR_NO_DEVICE, "no sm_100 device");
     return launch_transpose_i8(src, ld_src, K, N, dst, K, static_cast<cudaStream_t>(stream));
+}
+
+int ckb_transpose_a_colmajor(const void* src, int64_t ld_src, int32_t M, int32_t K, int32_t elem_bytes, void* dst, void* stream)
+{
+    if(!src || !dst || M < 0 || K < 0 || ld_src < M || (elem_bytes != 1 && elem_bytes != 2)) return set_error(CKB_ERR_INVALID, "bad transpose arguments");
+    if(!device_info().ok) return set_error(CKB_ERR_NO_DEVICE, "no sm_100 device");
+    // src is [K rows][M cols] with pitch ld_src; dst[m * K + k]
+    return elem_bytes == 2 ? launch_transpose_16(src, ld_src, K, M, dst, K, static_cast<cudaStream_t>(stream))
+                           : launch_transpose_i8(src, ld_src, K, M, dst, K, static_cast<cudaStream_t>(stream));
 }
 
 uint64_t ckb_prepack_b_int4_bytes(int32_t N, int32_t K)

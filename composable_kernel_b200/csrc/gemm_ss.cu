@@ -478,6 +478,8 @@ int plan_gemm_ss(const ckb_gemm_problem& p, ckb_gemm_plan& plan)
     const int pair_tiles = ((p.M + SS2_BM - 1) / SS2_BM) * num_n_blk;
     // (measured on B200, tests/ss_pair_probe.py: int8 gains 6-12 % from the pair, bf16/fp16 is level or slower, so 16-bit stays 1-CTA)
     sp->pair = i8 && p.M >= 2 * SS2_BM && pair_tiles >= sms / 2;
+    if(p.flags & CKB_FLAG_SS_1CTA) sp->pair = 0;
+    if(p.flags & CKB_FLAG_SS_2CTA) sp->pair = 1;
     if(const char* e = getenv("CKB_SS_2CTA")) sp->pair = atoi(e) != 0;
     if(sp->pair) plan.grid = 2 * std::max(1, std::min(sms / 2, pair_tiles));
     else plan.grid = std::max(1, std::min(sms, num_m_blk * num_n_blk));

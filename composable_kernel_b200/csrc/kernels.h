@@ -69,6 +69,7 @@ int run_grouped(const ckb_gemm_problem& proto, const void* dev_args, int group_c
 // ---- pre-pack ---------------------------------------------------------------------------------
 int launch_prepack_u8(const void* src, void* dst, long long n, cudaStream_t stream);
 int launch_prepack_int4(const void* src, long long sk, long long sn, int N, int K, void* dst, cudaStream_t stream);
+int launch_transpose_16(const void* src, long long ld_src, int rows, int cols, void* dst, long long ld_dst, cudaStream_t stream);
 int launch_transpose_i8(const void* src, long long ld_src, int rows, int cols, void* dst, long long ld_dst, cudaStream_t stream);
 
 } // namespace ckb

@@ -76,7 +76,35 @@ __global__ void transpose_i8_kernel(const uint8_t* __restrict__ src, long long l
     }
 }
 
+// 16-bit elements: dst[c * ld_dst + r] = src[r * ld_src + c]  (column-major A -> row-major A, per call)
+__global__ void transpose_16_kernel(const uint16_t* __restrict__ src, long long ld_src, int rows, int cols, uint16_t* __restrict__ dst,
+                                    long long ld_dst)
+{
+    __shared__ uint16_t tile[64][66];
+    const int r0 = blockIdx.y * 64, c0 = blockIdx.x * 64;
+    for(int i = threadIdx.y; i < 64; i += blockDim.y)
+    {
+        const int r = r0 + i, c = c0 + threadIdx.x;
+        tile[i][threadIdx.x] = (r < rows && c < cols) ? src[(long long)r * ld_src + c] : uint16_t(0);
+    }
+    __syncthreads();
+    for(int i = threadIdx.y; i < 64; i += blockDim.y)
+    {
+        const int c = c0 + i, r = r0 + threadIdx.x;
+        if(c < cols && r < rows) dst[(long long)c * ld_dst + r] = tile[threadIdx.x][i];
+    }
+}
+
 } // namespace
+
+int launch_transpose_16(const void* src, long long ld_src, int rows, int cols, void* dst, long long ld_dst, cudaStream_t stream)
+{
+    if(rows <= 0 || cols <= 0) return CKB_OK;
+    dim3 grid((cols + 63) / 64, (rows + 63) / 64), block(64, 8);
+    transpose_16_kernel<<<grid, block, 0, stream>>>(static_cast<const uint16_t*>(src), ld_src, rows, cols, static_cast<uint16_t*>(dst), ld_dst);
+    CKB_CUDA_CHECK(cudaGetLastError());
+    return CKB_OK;
+}
 
 int launch_prepack_u8(const void* src, void* dst, long long n, cudaStream_t stream)
 {

@@ -73,6 +73,11 @@ struct DeviceOperationInstanceFactory<
             op_ptrs.push_back(std::make_unique<DeviceGemmMultipleABD_Xdl_CShuffle<AsLayout, BsLayout, DsLayout, ELayout, AsDataType,
                                                                                   BsDataType, F32, F32, DsDataType, EDataType, AOp, BOp,
                                                                                   CDEOp>>());
+            // second instance: the two-pass prefill form (dequant pass into workspace + dense tcgen05 GEMM) next to the fused kernel;
+            // it serves M > 64 only and needs GetWorkSpaceSize() bytes
+            op_ptrs.push_back(std::make_unique<DeviceGemmMultipleABD_Sm100<AsLayout, BsLayout, DsLayout, ELayout, AsDataType, BsDataType, F32, F32,
+                                                                           DsDataType, EDataType, AOp, BOp, CDEOp, GemmSpecialization::Default,
+                                                                           CKB_FLAG_PREFILL_TWO_PASS>>());
         }
         return op_ptrs;
     }

@@ -21,6 +21,12 @@ struct DeviceOperationInstanceFactory<
         std::vector<std::unique_ptr<DeviceOp>> op_ptrs;
         op_ptrs.push_back(std::make_unique<DeviceGemmMultipleD_Xdl_CShuffle<ALayout, BLayout, DsLayout, ELayout, I8, I8, I32, I32,
                                                                             DsDataType, EDataType, PassThrough, PassThrough, CDEOp>>());
+        // the two tcgen05 tilings as explicit instances (the default instance above picks per shape): 128x256 tiles, one CTA each,
+        // and 256x256 tiles per CTA pair (cta_group::2) -- a real trade-off on this part that the caller can time
+        op_ptrs.push_back(std::make_unique<DeviceGemmMultipleD_Sm100<ALayout, BLayout, DsLayout, ELayout, I8, I8, I32, I32, DsDataType, EDataType,
+                                                                     PassThrough, PassThrough, CDEOp, GemmSpecialization::Default, CKB_FLAG_SS_1CTA>>());
+        op_ptrs.push_back(std::make_unique<DeviceGemmMultipleD_Sm100<ALayout, BLayout, DsLayout, ELayout, I8, I8, I32, I32, DsDataType, EDataType,
+                                                                     PassThrough, PassThrough, CDEOp, GemmSpecialization::Default, CKB_FLAG_SS_2CTA>>());
         return op_ptrs;
     }
 };

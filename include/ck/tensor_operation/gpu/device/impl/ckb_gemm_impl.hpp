@@ -82,6 +82,31 @@ struct GemmArgument : public BaseArgument
     // the transpose on the StreamConfig's stream -- a snapshot of the weight at that moment: call SetWorkSpacePointer again
     // after changing B.  A client that never supplies a workspace (the reference's client_example/30 does not) still runs:
     // the first Run allocates the copy itself and transposes on the run stream (not graph-capturable; documented fallback).
+    // Column-major A (CK's km_*): activations change every call, so every Run transposes A on the launch stream into workspace
+    // bytes reported by GetWorkSpaceSize (same fallback as above when the client supplies none); the GEMM then reads row-major A.
+    const void* colmajor_a = nullptr;
+    int64_t colmajor_lda   = 0;
+    void* a_slot           = nullptr;
+    std::shared_ptr<void> own_a;
+    size_t ElemBytesA() const { return (problem.a_dtype == CKB_I8 || problem.a_dtype == CKB_U8) ? 1 : 2; }
+    size_t TransposeABytes() const { return colmajor_a ? Align256(size_t(problem.M) * problem.K * ElemBytesA()) : 0; }
+    void DeferColMajorA()
+    {
+        colmajor_a   = problem.a;
+        colmajor_lda = problem.lda;
+        problem.lda = problem.K; problem.a_layout = CKB_ROW;   // validated / planned as the row-major problem it becomes
+    }
+    void BindASlot(void* slot)
+    {
+        a_slot    = slot;
+        problem.a = slot;
+        if(b_ready) Query();
+    }
+    void TransposeA(cudaStream_t stream) const
+    {
+        if(ckb_transpose_a_colmajor(colmajor_a, colmajor_lda, problem.M, problem.K, int(ElemBytesA()), a_slot, stream) != CKB_OK)
+            throw std::runtime_error(std::string("ckb_transpose_a_colmajor: ") + ckb_last_error());
+    }
     const void* rowmajor_b = nullptr;
     int64_t rowmajor_ld    = 0;
     bool b_ready           = true;
@@ -160,7 +185,16 @@ struct GemmInvoker : public BaseInvoker
             a.own_b = std::shared_ptr<void>(t, [](void* q) { cudaFree(q); });
             a.PrepareB(t, sc.stream_id_);
         }
+        if(arg.colmajor_a && !arg.a_slot)
+        {
+            auto& a = const_cast<GemmArgument&>(arg);
+            void* t = nullptr;
+            cuda_check(cudaMalloc(&t, a.TransposeABytes()), "cudaMalloc(row-major copy of A; supply a workspace to avoid this)");
+            a.own_a = std::shared_ptr<void>(t, [](void* q) { cudaFree(q); });
+            a.BindASlot(t);
+        }
         auto launch = [&]() {
+            if(arg.colmajor_a) arg.TransposeA(sc.stream_id_);
             const int rc = ckb_gemm_run(&arg.problem, &arg.plan, const_cast<GemmArgument&>(arg).Workspace(), sc.stream_id_);
             if(rc != CKB_OK) throw std::runtime_error(std::string("ckb_gemm_run: ") + ckb_last_error());
         };
@@ -192,7 +226,8 @@ inline size_t workspace_size(const BaseArgument* p)
     const auto* a = dynamic_cast<const GemmArgument*>(p);
     if(!a) return 0;
     const size_t kbytes = size_t(a->plan.workspace_bytes); // stream-K partial sums (decode-shaped int8-weight problems)
-    return a->rowmajor_b ? GemmArgument::Align256(kbytes) + a->RepackBytes() : kbytes;
+    if(!a->rowmajor_b && !a->colmajor_a) return kbytes;
+    return GemmArgument::Align256(kbytes) + a->RepackBytes() + a->TransposeABytes();
 }
 inline void set_workspace(BaseArgument* p_arg, void* p_workspace, const StreamConfig& sc)
 {
@@ -201,7 +236,9 @@ inline void set_workspace(BaseArgument* p_arg, void* p_workspace, const StreamCo
     if(!a || !p_workspace) return;
     const size_t kbytes = size_t(a->plan.workspace_bytes);
     if(kbytes) cuda_check(cudaMemsetAsync(p_workspace, 0, kbytes, sc.stream_id_), "cudaMemsetAsync(workspace)");
-    if(a->rowmajor_b) a->PrepareB(static_cast<char*>(p_workspace) + GemmArgument::Align256(kbytes), sc.stream_id_);
+    char* extra = static_cast<char*>(p_workspace) + GemmArgument::Align256(kbytes);
+    if(a->rowmajor_b) a->PrepareB(extra, sc.stream_id_);
+    if(a->colmajor_a) a->BindASlot(extra + a->RepackBytes());
 }
 
 template <typename Op, typename = void>

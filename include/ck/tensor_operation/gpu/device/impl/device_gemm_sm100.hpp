@@ -46,6 +46,10 @@ inline std::string type_string(const char* cls, const GemmArgument* a = nullptr)
     return s + ">";
 }
 // null-safe downcast of the type-erased argument (the reference dereferences dynamic_cast unchecked)
+inline const char* flags_tag(uint32_t f)
+{
+    return (f & CKB_FLAG_SS_1CTA) ? "[1cta]" : (f & CKB_FLAG_SS_2CTA) ? "[2cta]" : (f & CKB_FLAG_PREFILL_TWO_PASS) ? "[two_pass]" : (f & CKB_FLAG_GEMV_SINGLE_PRODUCER) ? "[single_producer]" : "";
+}
 inline const GemmArgument& checked(const BaseArgument* p)
 {
     const auto* a = dynamic_cast<const GemmArgument*>(p);
@@ -59,7 +63,7 @@ inline const GemmArgument& checked(const BaseArgument* p)
 template <typename ALayout, typename BLayout, typename CLayout, typename ADataType, typename BDataType,
           typename ScaleDataType, typename CDataType, typename AccDataType, typename CShuffleDataType,
           typename AElementwiseOperation, typename BElementwiseOperation, typename CElementwiseOperation,
-          GemmSpecialization GemmSpec = GemmSpecialization::Default>
+          GemmSpecialization GemmSpec = GemmSpecialization::Default, uint32_t KernelFlags = 0>
 struct DeviceFpAintBGemm_Sm100
     : public DeviceGemm_dequantB<ALayout, BLayout, CLayout, ADataType, BDataType, CDataType, AElementwiseOperation,
                                  BElementwiseOperation, CElementwiseOperation>
@@ -80,6 +84,7 @@ struct DeviceFpAintBGemm_Sm100
         p.b_op = CKB_BOP_FPAINTB; p.s_dtype = ckb_detail::dtype_of<ScaleDataType>(); p.scale = p_scale;
         p.cde_op = CElementwiseOperation::kCkbCde;
         p.e_dtype = ckb_detail::dtype_of<CDataType>(); p.e = p_c; p.lde = StrideC;
+        p.flags = KernelFlags;
         arg.Query();
         return arg;
     }
@@ -105,7 +110,7 @@ struct DeviceFpAintBGemm_Sm100
         ckb_detail::set_workspace(p, ws, sc);
     }
     virtual const char* ClassName() const { return "DeviceFpAintBGemm_Sm100"; }
-    std::string GetTypeString() const override { return ckb_detail::type_string(ClassName()); }
+    std::string GetTypeString() const override { return ckb_detail::type_string(ClassName()) + ckb_detail::flags_tag(KernelFlags); }
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -113,7 +118,7 @@ struct DeviceFpAintBGemm_Sm100
 template <typename AsLayout, typename BsLayout, typename DsLayout, typename ELayout, typename AsDataType,
           typename BsDataType, typename AccDataType, typename CShuffleDataType, typename DsDataType, typename EDataType,
           typename AElementwiseOperation, typename BElementwiseOperation, typename CDEElementwiseOperation,
-          GemmSpecialization GemmSpec = GemmSpecialization::Default>
+          GemmSpecialization GemmSpec = GemmSpecialization::Default, uint32_t KernelFlags = 0>
 struct DeviceGemmMultipleABD_Sm100
     : public DeviceGemmMultipleABD<AsLayout, BsLayout, DsLayout, ELayout, AsDataType, BsDataType, DsDataType, EDataType,
                                    AElementwiseOperation, BElementwiseOperation, CDEElementwiseOperation>
@@ -156,9 +161,11 @@ struct DeviceGemmMultipleABD_Sm100
         p.cde_scale = ckb_detail::cde_scale_of(cde);
         p.act = ckb_detail::cde_act_of<CDEElementwiseOperation>();
         p.e_dtype = ckb_detail::dtype_of<EDataType>(); p.e = p_e; p.lde = StrideE;
+        p.flags = KernelFlags;
+        if(p.a_layout == CKB_COL && arg.why.empty()) arg.DeferColMajorA(); // km_*: transposed on the launch stream in front of every Run
         if(p.b_layout == CKB_ROW && p.b_dtype == CKB_I8 && arg.why.empty())
             arg.DeferRowMajorB(); // mk_kn_mn: no allocation and no launch here (see GemmArgument::DeferRowMajorB)
-        if(arg.why.empty()) arg.Query();
+        else if(arg.why.empty()) arg.Query();
         return arg;
     }
     static Invoker MakeInvoker() { return Invoker{}; }
@@ -182,7 +189,7 @@ struct DeviceGemmMultipleABD_Sm100
         ckb_detail::set_workspace(p, ws, sc);
     }
     virtual const char* ClassName() const { return "DeviceGemmMultipleABD_Sm100"; }
-    std::string GetTypeString() const override { return ckb_detail::type_string(ClassName()); }
+    std::string GetTypeString() const override { return ckb_detail::type_string(ClassName()) + ckb_detail::flags_tag(KernelFlags); }
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -190,7 +197,7 @@ struct DeviceGemmMultipleABD_Sm100
 template <typename ALayout, typename BLayout, typename DsLayout, typename ELayout, typename ADataType, typename BDataType,
           typename AccDataType, typename CShuffleDataType, typename DsDataType, typename EDataType,
           typename AElementwiseOperation, typename BElementwiseOperation, typename CDEElementwiseOperation,
-          GemmSpecialization GemmSpec = GemmSpecialization::Default>
+          GemmSpecialization GemmSpec = GemmSpecialization::Default, uint32_t KernelFlags = 0>
 struct DeviceGemmMultipleD_Sm100
     : public DeviceGemmMultipleD<ALayout, BLayout, DsLayout, ELayout, ADataType, BDataType, DsDataType, EDataType,
                                  AElementwiseOperation, BElementwiseOperation, CDEElementwiseOperation>
@@ -217,6 +224,7 @@ struct DeviceGemmMultipleD_Sm100
         p.cde_scale = ckb_detail::cde_scale_of(cde);
         p.act = ckb_detail::cde_act_of<CDEElementwiseOperation>();
         p.e_dtype = ckb_detail::dtype_of<EDataType>(); p.e = p_e; p.lde = StrideE;
+        p.flags = KernelFlags;
         arg.Query();
         return arg;
     }
@@ -240,7 +248,7 @@ struct DeviceGemmMultipleD_Sm100
         ckb_detail::set_workspace(p, ws, sc);
     }
     virtual const char* ClassName() const { return "DeviceGemmMultipleD_Sm100"; }
-    std::string GetTypeString() const override { return ckb_detail::type_string(ClassName()); }
+    std::string GetTypeString() const override { return ckb_detail::type_string(ClassName()) + ckb_detail::flags_tag(KernelFlags); }
 };
 
 

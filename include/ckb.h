@@ -99,10 +99,16 @@ typedef enum ckb_act { CKB_ACT_PASSTHROUGH = 0, CKB_ACT_RELU = 1 } ckb_act;
 enum {
     CKB_FLAG_BF16_RNE = 1 << 0, /* round bf16 outputs to nearest-even instead of CK's truncation
                                   (type_convert.hpp:53-64 vs :508-549); default = truncation */
-    CKB_FLAG_FIXED_K_ORDER = 1 << 1 /* [EXT] W4A16 decode (M <= 64): make the fp32 summation order over K independent of N, of the
+    CKB_FLAG_FIXED_K_ORDER = 1 << 1, /* [EXT] W4A16 decode (M <= 64): make the fp32 summation order over K independent of N, of the
                                   grid and of the shard a problem is cut into, so that G column shards + all-gather reproduce
                                   the single-GPU E bit for bit.  Without it the planner picks the fastest warp
                                   grid per shape and two different N may differ in the last bit of a few outputs. */
+    /* kernel-choice overrides: the library picks per shape by default; the instance factories register the alternatives as
+       separate instances so that a profiler can time them (the reference's run-every-instance-keep-the-best loop) */
+    CKB_FLAG_SS_1CTA   = 1 << 2,            /* dense / int8 tcgen05 kernel: one CTA per 128x256 tile */
+    CKB_FLAG_SS_2CTA   = 1 << 3,            /* ... CTA pair (cta_group::2) per 256x256 tile */
+    CKB_FLAG_PREFILL_TWO_PASS = 1 << 4,     /* weight-quantized prefill: dequant pass into workspace + dense GEMM (round-1 form) */
+    CKB_FLAG_GEMV_SINGLE_PRODUCER = 1 << 5  /* W4A16 decode: single-producer kernel (wq_gemv) instead of the rotating-producer one */
 };
 
 #define CKB_MAX_D 2
@@ -203,6 +209,10 @@ int ckb_prepack_b_u8(const void* src_i8, void* dst_u8, int64_t n, void* stream);
 /* Row-major int8 B[k,n] = src[k*ld_src + n] (CK's mk_kn_mn) -> K-major dst[n*K + k], the layout the kernels
    stream.  One-time weight transform, device pointers. */
 int ckb_prepack_b_rowmajor_i8(const void* src_kn, int64_t ld_src, int32_t K, int32_t N, void* dst_nk, void* stream);
+
+/* Column-major A (CK's km_*: A[m,k] = src[k*ld_src + m], 16-bit or 8-bit elements) -> row-major dst[m*K + k].  Activations change
+   every call, so the C++ operators run this on the launch stream in front of every GEMM, into caller-supplied workspace. */
+int ckb_transpose_a_colmajor(const void* src_km, int64_t ld_src, int32_t M, int32_t K, int32_t elem_bytes, void* dst_mk, void* stream);
 
 /* [EXT] 4-bit codes, one per byte, logical B[k,n] = src[k*src_sk + n*src_sn] (device) ->
    tile-major packed layout consumed by the W4A16 kernels.  dst needs ckb_prepack_b_int4_bytes(). */

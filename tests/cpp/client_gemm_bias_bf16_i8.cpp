@@ -2,7 +2,7 @@
 // DeviceGemmMultipleABD<Row; {Row|Col,..}; Row; Row; BF16; {I8,BF16}; BF16; BF16; PassThrough, Multiply, Add>, run every
 // instance, print the best.  The reference client does no verification; this port adds the host check of
 // example/60_gemm_multi_ABD (b = Multiply(b0,b1) into bf16, ReferenceGemm, then Add) so it doubles as a test.
-// usage: client_gemm_bias_bf16_i8 [M N K] [b_layout: 0 = Row (mk_kn_mn), 1 = Col (mk_nk_mn)] [verify] [cde: add|add_gelu]
+// usage: client_gemm_bias_bf16_i8 [M N K] [layout: 0 = mk_kn_mn, 1 = mk_nk_mn, 2 = km_kn_mn (column-major A)] [verify] [cde: add|add_gelu]
 #include <cstring>
 #include <iostream>
 
@@ -18,13 +18,15 @@ using Row = ck::tensor_layout::gemm::RowMajor; using Col = ck::tensor_layout::ge
 using PassThrough = ck::tensor_operation::element_wise::PassThrough;
 using Multiply = ck::tensor_operation::element_wise::Multiply;
 
-template <typename BLayout, typename CDEOp>
+template <typename BLayout, typename CDEOp, typename ALayout = Row>
 int run(ck::index_t M, ck::index_t N, ck::index_t K, bool verify)
 {
     using namespace ck::literals;
     constexpr bool b_row = std::is_same_v<BLayout, Row>;
-    const ck::index_t StrideA = K, StrideB = b_row ? N : K, StrideD = 0, StrideE = N; // bias broadcast along M
-    Tensor<BF16> a0_m_k(HostTensorDescriptor({std::size_t(M), std::size_t(K)}, {std::size_t(StrideA), 1_uz}));
+    constexpr bool a_row = std::is_same_v<ALayout, Row>;
+    const ck::index_t StrideA = a_row ? K : M, StrideB = b_row ? N : K, StrideD = 0, StrideE = N; // bias broadcast along M
+    Tensor<BF16> a0_m_k(a_row ? HostTensorDescriptor({std::size_t(M), std::size_t(K)}, {std::size_t(StrideA), 1_uz})
+                              : HostTensorDescriptor({std::size_t(M), std::size_t(K)}, {1_uz, std::size_t(StrideA)}));
     Tensor<I8> b0_k_n(b_row ? HostTensorDescriptor({std::size_t(K), std::size_t(N)}, {std::size_t(StrideB), 1_uz})
                             : HostTensorDescriptor({std::size_t(K), std::size_t(N)}, {1_uz, std::size_t(StrideB)}));
     Tensor<BF16> b1_k_n(HostTensorDescriptor({std::size_t(K), std::size_t(N)}, {0_uz, 1_uz}));
@@ -40,7 +42,7 @@ int run(ck::index_t M, ck::index_t N, ck::index_t K, bool verify)
     a_buf.ToDevice(a0_m_k.mData.data()); b0_buf.ToDevice(b0_k_n.mData.data()); b1_buf.ToDevice(b1_k_n.mData.data());
     d_buf.ToDevice(d_m_n.mData.data());
 
-    using DeviceOp = ck::tensor_operation::device::DeviceGemmMultipleABD<ck::Tuple<Row>, ck::Tuple<BLayout, BLayout>, ck::Tuple<Row>, Row,
+    using DeviceOp = ck::tensor_operation::device::DeviceGemmMultipleABD<ck::Tuple<ALayout>, ck::Tuple<BLayout, BLayout>, ck::Tuple<Row>, Row,
                                                                          ck::Tuple<BF16>, ck::Tuple<I8, BF16>, ck::Tuple<BF16>, BF16,
                                                                          PassThrough, Multiply, CDEOp>;
     const auto op_ptrs = ck::tensor_operation::device::instance::DeviceOperationInstanceFactory<DeviceOp>::GetInstances();
@@ -52,6 +54,9 @@ int run(ck::index_t M, ck::index_t N, ck::index_t K, bool verify)
                                                         {d_buf.GetDeviceBuffer()}, e_buf.GetDeviceBuffer(), M, N, K, {StrideA},
                                                         {StrideB, 0}, {StrideD}, StrideE, PassThrough{}, Multiply{}, CDEOp{});
         auto invoker_ptr = op_ptr->MakeInvokerPointer();
+        // row-major B and column-major A need workspace (K-major copy of the weight / row-major copy of the activations)
+        DeviceMem ws(op_ptr->GetWorkSpaceSize(argument_ptr.get()));
+        if(ws.GetDeviceBuffer()) op_ptr->SetWorkSpacePointer(argument_ptr.get(), ws.GetDeviceBuffer());
         if(!op_ptr->IsSupportedArgument(argument_ptr.get())) { std::cout << op_ptr->GetTypeString() << " does not support this problem" << std::endl; continue; }
         ++found;
         const float ave_time = invoker_ptr->Run(argument_ptr.get(), StreamConfig{nullptr, true, 0, 3, 10});
@@ -85,6 +90,7 @@ int main(int argc, char* argv[])
     if(argc >= 6) verify = std::atoi(argv[5]);
     if(argc >= 7) cde = argv[6];
     using Add = ck::tensor_operation::element_wise::Add; using AddFastGelu = ck::tensor_operation::element_wise::AddFastGelu;
+    if(b_col == 2) return !std::strcmp(cde, "add_gelu") ? run<Row, AddFastGelu, Col>(M, N, K, verify) : run<Row, Add, Col>(M, N, K, verify);
     if(!std::strcmp(cde, "add_gelu")) return b_col ? run<Col, AddFastGelu>(M, N, K, verify) : run<Row, AddFastGelu>(M, N, K, verify);
     return b_col ? run<Col, Add>(M, N, K, verify) : run<Row, Add>(M, N, K, verify);
 }

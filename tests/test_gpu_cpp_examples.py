@@ -14,6 +14,8 @@ CASES = [
     ("example_fp16int8_gemm", ["1", "2", "0", "64", "256", "1024"]),            # real-valued init
     ("client_gemm_bias_bf16_i8", ["64", "512", "256", "1", "1", "add"]),        # client 30, mk_nk_mn
     ("client_gemm_bias_bf16_i8", ["48", "256", "384", "0", "1", "add_gelu"]),   # mk_kn_mn (row-major B) + AddFastGelu
+    ("client_gemm_bias_bf16_i8", ["200", "512", "256", "2", "1", "add"]),       # km_kn_mn: column-major A (prefill rows)
+    ("client_gemm_bias_bf16_i8", ["16", "256", "512", "2", "1", "add_gelu"]),   # km_kn_mn, decode rows
     ("example_gemm_quantization_int8", ["0", "256", "512", "384"]),
     ("example_gemm_quantization_int8", ["1", "256", "512", "384"]),
     ("example_gemm_quantization_int8", ["2", "384", "256", "512"]),
