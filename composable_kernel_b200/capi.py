@@ -19,6 +19,7 @@ F32, F16, BF16, I8, U8, I32, I4 = range(7)
 ROW, COL, PREPACKED = 0, 1, 2
 BOP_PASSTHROUGH, BOP_MULTIPLY, BOP_FPAINTB, BOP_GROUP, BOP_GROUP_RTN = range(5)
 FLAG_BF16_RNE, FLAG_FIXED_K_ORDER = 1, 2
+FLAG_SS_1CTA, FLAG_SS_2CTA, FLAG_PREFILL_TWO_PASS, FLAG_GEMV_SINGLE_PRODUCER, FLAG_INPUTS_READY = 4, 8, 16, 32, 64
 (CDE_PASSTHROUGH, CDE_ADD, CDE_FASTGELU, CDE_ADD_FASTGELU, CDE_MULTIPLY, CDE_MULTIPLY_ADD,
  CDE_MULTIPLY_FASTGELU, CDE_MULTIPLY_ADD_FASTGELU, CDE_MULTIPLY_MULTIPLY, CDE_ACT_MUL_CLAMP,
  CDE_ADD_ACT_MUL_CLAMP, CDE_ACT_MUL2_CLAMP, CDE_ADD_ACT_MUL2_CLAMP) = range(13)
@@ -87,11 +88,14 @@ def lib():
         l.ckb_prepack_b_int4_bytes.restype = C.c_uint64
         l.ckb_prepack_b_int4.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_void_p,
                                          C.c_void_p]
-        l.ckb_tile_coord.argtypes = [C.c_int32] * 4 + [C.POINTER(C.c_int32)] * 2
-        l.ckb_streamk_range.argtypes = [C.c_int64, C.c_int32, C.c_int32, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
-        l.ckb_gemv_schedule.argtypes = [C.c_int32] * 6 + [C.POINTER(C.c_int32)]
-        l.ckb_transpose_a_colmajor.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
-        l.ckb_peer_wait.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+        if os.environ.get("CKB_LIB") and not hasattr(l, "ckb_tile_coord"):
+            pass  # an older debug build selected for an A/B measurement: the newer entry points are simply absent
+        else:
+            l.ckb_tile_coord.argtypes = [C.c_int32] * 4 + [C.POINTER(C.c_int32)] * 2
+            l.ckb_streamk_range.argtypes = [C.c_int64, C.c_int32, C.c_int32, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+            l.ckb_gemv_schedule.argtypes = [C.c_int32] * 6 + [C.POINTER(C.c_int32)]
+            l.ckb_transpose_a_colmajor.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
+            l.ckb_peer_wait.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
         l.ckb_grouped_gemm_arg_bytes.argtypes = [C.c_int32, C.c_int32]
         l.ckb_grouped_gemm_arg_bytes.restype = C.c_uint64
         l.ckb_grouped_gemm_query.argtypes = [C.POINTER(GemmProblem), C.c_int32]

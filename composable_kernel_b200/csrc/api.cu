@@ -214,7 +214,7 @@ int ckb_gemm_query(const ckb_gemm_problem* pp, ckb_gemm_plan* plan)
     if(p.num_peers < 0 || p.num_peers > CKB_MAX_PEERS) return set_error(CKB_ERR_INVALID, "num_peers out of range");
     if(p.num_peers > 0)
     {
-        if(!w4 || p.M > 32) return unsupported(plan, "the fused all-gather epilogue is served by the W4A16 decode kernel (M <= 32)");
+        if(p.b_op != CKB_BOP_GROUP || p.M > 32) return unsupported(plan, "the fused all-gather epilogue is served by the W4A16 decode kernel (CKB_BOP_GROUP, M <= 32)");
         if(p.peer_rank < 0 || p.peer_rank >= p.num_peers) return set_error(CKB_ERR_INVALID, "peer_rank out of range");
         for(int g = 0; g < p.num_peers; ++g)
             if(!p.e_peer[g] || !p.flag_peer[g]) return set_error(CKB_ERR_INVALID, "null peer pointer");

@@ -33,7 +33,7 @@ int launch_gemv2_variant(bool f16, int nt, int gw, int kbu, const G2Plan* gp, co
 // ckb_gemv_schedule): how the n16 channel groups and the K range are cut into (CTA, pass, stage, warp) work.
 int schedule_wq_gemv2(int M, int N, int K, bool zp, int sms, G2Sched& s, int mode)
 {
-    const bool fixed = mode & 1, rtn = mode & 2;
+    const bool fixed = mode & 1, rtn = (mode & 2) || (mode & 4); // bit 2 (peer-store epilogue): 128-k units like RTN, fp32-scale numerics
     if(M < 1 || M > 32) return set_error(CKB_ERR_UNSUPPORTED, "W4 decode kernel handles 1 <= M <= 32 per launch");
     s.nt = M <= 8 ? 1 : (M <= 16 ? 2 : 4);
     s.rb = s.nt == 1 ? (M <= 1 ? 1 : (M <= 2 ? 2 : (M <= 4 ? 4 : 8))) : 8 * s.nt;
@@ -128,7 +128,7 @@ int plan_wq_gemv2(const ckb_gemm_problem& p, ckb_gemm_plan& plan)
     const bool zp  = p.zero != nullptr;
     const int sms  = device_info().sm_count > 0 ? device_info().sm_count : 148;
     G2Sched s{};
-    const int mode = ((p.flags & CKB_FLAG_FIXED_K_ORDER) ? 1 : 0) | (p.b_op == CKB_BOP_GROUP_RTN ? 2 : 0);
+    const int mode = ((p.flags & CKB_FLAG_FIXED_K_ORDER) ? 1 : 0) | (p.b_op == CKB_BOP_GROUP_RTN ? 2 : 0) | (p.num_peers > 0 ? 4 : 0);
     if(int rc = schedule_wq_gemv2(p.M, p.N, p.K, zp, sms, s, mode)) return rc;
     gp->nt = s.nt; gp->gw = s.gw; gp->passes = s.passes; gp->slot_q = s.slot_q; gp->slot_r = s.slot_r; gp->g_hi = s.g_hi;
     gp->wn_log2 = s.wn_log2; gp->kbu = s.kbu; gp->upw = s.upw; gp->n_chunks = s.n_chunks; gp->ring = s.ring; gp->stage_bytes = s.stage_bytes;
@@ -231,6 +231,10 @@ int run_wq_gemv2(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStrea
     a.zero_const = p.zero_const;
     a.has_zero   = p.zero != nullptr;
     a.rtn        = gp->rtn;
+    // the optional paths live in the EXT instantiation (128-k units, fp32-scale numerics): peers force it through the schedule
+    // (mode bit 2), the inputs-ready hint is honoured when the plan happens to use 128-k units and is ignored otherwise
+    a.nodep      = ((p.flags & CKB_FLAG_INPUTS_READY) && gp->kbu == 2 && !gp->rtn) ? 1 : 0;
+    a.ext        = (a.nodep || p.num_peers > 0) ? 1 : 0;
     {
         // programmatic dependent launch pays inside a CUDA graph (PDL edges: the next kernel's prologue and weight prefill
         // overlap this one) but an EAGER launch with the attribute costs ~20 us of host time against ~6 us without

@@ -54,6 +54,8 @@ struct G2Args
     int zero_const;
     int has_zero;
     int pdl;        // launch with programmatic stream serialization
+    int ext;        // launch the EXT instantiation (peers or nodep requested; 128-k units, fp32-scale numerics)
+    int nodep;      // CKB_FLAG_INPUTS_READY (EXT instantiation): do not wait for the previous grid before reading A; wait before exit
     int rtn;        // CKB_BOP_GROUP_RTN: (q - zp) * s rounded once into A's type before the MMA (RTN kernel instantiation)
     int dbg;        // debug knobs (CKB_GEMV_DBG): 1 = skip the math, 8 = skip the copies and waits
     int peer_rank;  // this rank's index among the peers
@@ -65,23 +67,33 @@ struct G2Args
     EpiParams ep;
 };
 
-static __device__ __forceinline__ void g2_store_e(const EpiParams& ep, void* e, long long off, float v)
-{
-    if(ep.e_dtype == CKB_BF16) static_cast<uint16_t*>(e)[off] = f32_to_bf16_bits(v, ep.flags);
-    else if(ep.e_dtype == CKB_F16) static_cast<__half*>(e)[off] = __float2half_rn(v);
-    else static_cast<float*>(e)[off] = v;
-}
-
-static __device__ __noinline__ void g2_store_one(const EpiParams& ep, int m, int n, float acc, int num_peers, void* const* e_peer)
+static __device__ __noinline__ void g2_store_one(const EpiParams& ep, int m, int n, float acc)
 {
     float d0 = 0.f, d1 = 0.f;
     if(ep.num_d > 0) d0 = load_d_f32(ep.d_dtype[0], ep.d[0], (long long)m * ep.d_sm[0] + (long long)n * ep.d_sn[0]);
     if(ep.num_d > 1) d1 = load_d_f32(ep.d_dtype[1], ep.d[1], (long long)m * ep.d_sm[1] + (long long)n * ep.d_sn[1]);
     const float v       = cde_apply_f32(ep, acc, d0, d1);
     const long long off = (long long)m * ep.lde + n;
-    if(num_peers == 0) g2_store_e(ep, ep.e, off, v);
-    else
-        for(int g = 0; g < num_peers; ++g) g2_store_e(ep, e_peer[g], off, v); // this rank's slot in every rank's gathered buffer
+    if(ep.e_dtype == CKB_BF16) static_cast<uint16_t*>(ep.e)[off] = f32_to_bf16_bits(v, ep.flags);
+    else if(ep.e_dtype == CKB_F16) static_cast<__half*>(ep.e)[off] = __float2half_rn(v);
+    else static_cast<float*>(ep.e)[off] = v;
+}
+
+// EXT instantiation only: the same element into this rank's slot of every rank's gathered buffer (fused all-gather, ckb.h)
+static __device__ __noinline__ void g2_store_peers(const EpiParams& ep, int m, int n, float acc, int num_peers, void* const* e_peer)
+{
+    float d0 = 0.f, d1 = 0.f;
+    if(ep.num_d > 0) d0 = load_d_f32(ep.d_dtype[0], ep.d[0], (long long)m * ep.d_sm[0] + (long long)n * ep.d_sn[0]);
+    if(ep.num_d > 1) d1 = load_d_f32(ep.d_dtype[1], ep.d[1], (long long)m * ep.d_sm[1] + (long long)n * ep.d_sn[1]);
+    const float v       = cde_apply_f32(ep, acc, d0, d1);
+    const long long off = (long long)m * ep.lde + n;
+    for(int g = 0; g < num_peers; ++g)
+    {
+        void* e = e_peer[g];
+        if(ep.e_dtype == CKB_BF16) static_cast<uint16_t*>(e)[off] = f32_to_bf16_bits(v, ep.flags);
+        else if(ep.e_dtype == CKB_F16) static_cast<__half*>(e)[off] = __float2half_rn(v);
+        else static_cast<float*>(e)[off] = v;
+    }
 }
 
 #ifdef CKB_ENABLE_TRACE
@@ -96,7 +108,10 @@ static __device__ __noinline__ void g2_store_one(const EpiParams& ep, int m, int
 #define G2_TV(k, v) do { } while(0)
 #endif
 
-template <int NT, int GW, int KBU, bool F16, bool ZP, bool RTN>
+// EXT = the instantiation with the optional paths compiled in (peer-store epilogue of the fused all-gather, CKB_FLAG_INPUTS_READY):
+// the kernel is so sensitive to its dynamic instruction count that even never-taken branches cost 2-5 % (A/B against the build
+// without them, profiles/r2_gemv_ab_ext.txt), so the default instantiation does not contain them.
+template <int NT, int GW, int KBU, bool F16, bool ZP, bool RTN, bool EXT>
 __global__ void __launch_bounds__(g2_threads(NT), 2)
 wq_gemv2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW0,
                 const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ CUtensorMap tmS0,
@@ -182,7 +197,7 @@ wq_gemv2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     }
     G2_T(1);
     ptx::pdl_launch_dependents();
-    ptx::pdl_wait_prior_grids();
+    if(!(EXT && args.nodep)) ptx::pdl_wait_prior_grids();
     G2_T(2);
     if(my_pre) issue_acts(warp, my_c);
 
@@ -379,7 +394,7 @@ wq_gemv2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                     red[warp * n_vec + (gi * NT + nt) * 32 + lane] =
                         make_float4(acc[gi][nt][0], acc[gi][nt][1], acc[gi][nt][2], acc[gi][nt][3]);
         __syncthreads();
-        const bool fast = ep.cde_op == CKB_CDE_PASSTHROUGH && (ep.e_dtype == CKB_BF16 || ep.e_dtype == CKB_F16) && args.num_peers == 0;
+        const bool fast = ep.cde_op == CKB_CDE_PASSTHROUGH && (ep.e_dtype == CKB_BF16 || ep.e_dtype == CKB_F16) && !(EXT && args.num_peers > 0);
         // thread -> (half h, vector v): the WK partial sums of a vector are added and stored by one thread
         const int n_out = sg * NT * 32;
         for(int o = tid; o < n_out; o += NW * 32)
@@ -407,12 +422,18 @@ wq_gemv2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                         static_cast<uint16_t*>(ep.e)[(long long)m * ep.lde + n] =
                             ep.e_dtype == CKB_BF16 ? f32_to_bf16_bits(vv[r], ep.flags) : __half_as_ushort(__float2half_rn(vv[r]));
                     else
-                        g2_store_one(ep, m, n, vv[r], (args.dbg & 32) ? 1 : args.num_peers, (args.dbg & 32) ? &args.e_peer[args.peer_rank] : args.e_peer);
+                        if(EXT && args.num_peers > 0)
+                            g2_store_peers(ep, m, n, vv[r], (args.dbg & 32) ? 1 : args.num_peers, (args.dbg & 32) ? &args.e_peer[args.peer_rank] : args.e_peer);
+                        else
+                            g2_store_one(ep, m, n, vv[r]);
                 }
             }
         }
     }
-    if(args.num_peers > 0 && !(args.dbg & 128))
+    // inputs were declared independent of the previous grid: keep completion order along the stream (a later kernel that waits for
+    // THIS grid must also be ordered after the one before it)
+    if(EXT && args.nodep) ptx::pdl_wait_prior_grids();
+    if(EXT && args.num_peers > 0 && !(args.dbg & 128))
     {
         // fused all-gather: every store of this CTA is ordered before its arrival on every rank's counter (CTA barrier, then
         // one thread: system-scope fence + release adds over NVLink); the consumer side is ckb_peer_wait
@@ -445,10 +466,10 @@ struct G2Plan
 // per-(dtype, NT) launchers: each lives in its own translation unit (wq_gemv2_inst.cu, -DGV_INST_F16 / -DGV_INST_NT)
 int launch_gemv2_variant(bool f16, int nt, int gw, int kbu, const G2Plan* gp, const G2Args& a, int grid, cudaStream_t stream);
 
-template <int NT, int GW, int KBU, bool F16, bool ZP, bool RTN>
+template <int NT, int GW, int KBU, bool F16, bool ZP, bool RTN, bool EXT>
 static int launch_gemv2(const G2Plan* gp, const G2Args& a, int grid, cudaStream_t stream)
 {
-    auto kfn = wq_gemv2_kernel<NT, GW, KBU, F16, ZP, RTN>;
+    auto kfn = wq_gemv2_kernel<NT, GW, KBU, F16, ZP, RTN, EXT>;
     // the opt-in is per device (cudaFuncSetAttribute applies to the current device only): one flag per device ordinal
     static unsigned long long attr_mask = 0;
     int dev = 0;

@@ -108,7 +108,12 @@ enum {
     CKB_FLAG_SS_1CTA   = 1 << 2,            /* dense / int8 tcgen05 kernel: one CTA per 128x256 tile */
     CKB_FLAG_SS_2CTA   = 1 << 3,            /* ... CTA pair (cta_group::2) per 256x256 tile */
     CKB_FLAG_PREFILL_TWO_PASS = 1 << 4,     /* weight-quantized prefill: dequant pass into workspace + dense GEMM (round-1 form) */
-    CKB_FLAG_GEMV_SINGLE_PRODUCER = 1 << 5  /* W4A16 decode: single-producer kernel (wq_gemv) instead of the rotating-producer one */
+    CKB_FLAG_GEMV_SINGLE_PRODUCER = 1 << 5, /* W4A16 decode: single-producer kernel (wq_gemv) instead of the rotating-producer one */
+    CKB_FLAG_INPUTS_READY = 1 << 6          /* [EXT] the caller asserts that A, D and the weights of THIS GEMM are not written by the
+                                               kernel launched just before it on the stream (e.g. the k / v projections after q, `up` after
+                                               `gate`: same layer input).  Under programmatic dependent launch (graph replay) the W4A16 decode
+                                               kernel then starts computing while its predecessor drains, and waits for the predecessor only
+                                               before it exits, so completion order along the stream is preserved.  No effect elsewhere. */
 };
 
 #define CKB_MAX_D 2
@@ -163,7 +168,7 @@ typedef struct ckb_gemm_problem {
        g's own kernels touch (both start at 0).  When the last CTA of the launch has finished (device-scope count on the own
        scratch word) it adds 1 (release, system scope) to the arrival counter of every rank; a rank's gathered buffer is
        complete when its counter has grown by G (ckb_peer_wait).  peer_rank = this rank's index in the arrays.
-       Served by the W4A16 decode kernel (M <= 32, GROUP / GROUP_RTN); other problems report unsupported. */
+       Served by the W4A16 decode kernel (CKB_BOP_GROUP, M <= 32); other problems report unsupported. */
     int32_t num_peers, peer_rank;
     void* e_peer[CKB_MAX_PEERS];
     void* flag_peer[CKB_MAX_PEERS];

@@ -82,7 +82,10 @@ def case_w4(M, N, K):
         packed = torch.randint(0, 256, (int(capi.lib().ckb_prepack_b_int4_bytes(N, K)),), dtype=torch.uint8, device="cuda")
         sc = (torch.rand(K // 128, N, device="cuda") * 0.01).bfloat16()
         e = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
-        lst.append(ops.GemmOp(a, packed, e, b_dtype=capi.I4, b_layout=capi.PREPACKED, b_op=BOP_W4(M), N=N, K=K,
+        # PERF_NODEP=n: every GEMM whose index is not a multiple of n declares its inputs independent of its predecessor
+        nd = int(os.environ.get("PERF_NODEP", 0))
+        fl = capi.FLAG_INPUTS_READY if nd and (len(lst) % nd) else 0
+        lst.append(ops.GemmOp(a, packed, e, flags=fl, b_dtype=capi.I4, b_layout=capi.PREPACKED, b_op=BOP_W4(M), N=N, K=K,
                               scale=sc, zero_const=8, group_size=128))
     lst = lst * int(os.environ.get("PERF_REPEAT", 1))   # longer graphs for small rotations
     us = timeit(lst, 5)
