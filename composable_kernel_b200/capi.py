@@ -19,7 +19,7 @@ F32, F16, BF16, I8, U8, I32, I4 = range(7)
 ROW, COL, PREPACKED = 0, 1, 2
 BOP_PASSTHROUGH, BOP_MULTIPLY, BOP_FPAINTB, BOP_GROUP, BOP_GROUP_RTN = range(5)
 FLAG_BF16_RNE, FLAG_FIXED_K_ORDER = 1, 2
-FLAG_SS_1CTA, FLAG_SS_2CTA, FLAG_PREFILL_TWO_PASS, FLAG_GEMV_SINGLE_PRODUCER, FLAG_INPUTS_READY = 4, 8, 16, 32, 64
+FLAG_SS_1CTA, FLAG_SS_2CTA, FLAG_PREFILL_TWO_PASS, FLAG_GEMV_SINGLE_PRODUCER, FLAG_INPUTS_READY, FLAG_W8_STREAMK = 4, 8, 16, 32, 64, 128
 (CDE_PASSTHROUGH, CDE_ADD, CDE_FASTGELU, CDE_ADD_FASTGELU, CDE_MULTIPLY, CDE_MULTIPLY_ADD,
  CDE_MULTIPLY_FASTGELU, CDE_MULTIPLY_ADD_FASTGELU, CDE_MULTIPLY_MULTIPLY, CDE_ACT_MUL_CLAMP,
  CDE_ADD_ACT_MUL_CLAMP, CDE_ACT_MUL2_CLAMP, CDE_ADD_ACT_MUL2_CLAMP) = range(13)

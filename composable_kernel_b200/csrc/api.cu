@@ -232,6 +232,7 @@ int ckb_gemm_query(const ckb_gemm_problem* pp, ckb_gemm_plan* plan)
     // GROUP_RTN (one rounding into A's type) by the fused tcgen05 kernel above 64 rows and by the RTN instantiation of the
     // HMMA kernel below.
     if((p.flags & CKB_FLAG_PREFILL_TWO_PASS) && p.M <= 64) return unsupported(plan, "the two-pass prefill instance serves M > 64");
+    if((p.flags & CKB_FLAG_W8_STREAMK) && (p.M > 64 || w4)) return unsupported(plan, "the stream-K decode instance serves int8 weights at M <= 64");
     if(p.M > 64 && p.K % 8 == 0 && p.b_op != CKB_BOP_GROUP)
     {
         // prefill-shaped: the fused TMA -> dequant -> tcgen05 pair kernel (no workspace).  CKB_PREFILL_TWO_PASS=1 selects the
@@ -267,6 +268,21 @@ int ckb_gemm_query(const ckb_gemm_problem* pp, ckb_gemm_plan* plan)
         plan->kernel_id = old_kernel ? KID_WQ_GEMV : KID_WQ_GEMV2;
         plan->supported = 1;
         return CKB_OK;
+    }
+    // int8-weight formats at decode sizes: the N-split HMMA kernel of the W4 path (K-major int8 streamed as [kb][row][64 B] boxes,
+    // 32 rows per launch, no workspace) when K is a whole number of 64-k blocks; the stream-K tcgen05 kernel otherwise and behind
+    // CKB_FLAG_W8_STREAMK / CKB_W8_DECODE=streamk (second factory instance)
+    {
+        const char* e8 = getenv("CKB_W8_DECODE");
+        const bool streamk = (p.flags & CKB_FLAG_W8_STREAMK) || (e8 && !strcmp(e8, "streamk"));
+        if(!streamk && p.K % 64 == 0 && p.M >= 1)
+        {
+            ckb_gemm_problem q = p;
+            q.M = std::min(p.M, 32);
+            const int rc = plan_wq_gemv2(q, *plan);
+            if(rc == CKB_OK) { plan->kernel_id = KID_WQ_GEMV2; plan->supported = 1; return CKB_OK; }
+            if(rc != CKB_ERR_UNSUPPORTED) return rc;
+        }
     }
     {
         // M <= 64: one pass of the stream-K decode kernel (larger M with K % 8 != 0: 64-row slabs of it)

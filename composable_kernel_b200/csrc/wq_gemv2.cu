@@ -33,7 +33,8 @@ int launch_gemv2_variant(bool f16, int nt, int gw, int kbu, const G2Plan* gp, co
 // ckb_gemv_schedule): how the n16 channel groups and the K range are cut into (CTA, pass, stage, warp) work.
 int schedule_wq_gemv2(int M, int N, int K, bool zp, int sms, G2Sched& s, int mode)
 {
-    const bool fixed = mode & 1, rtn = (mode & 2) || (mode & 4); // bit 2 (peer-store epilogue): 128-k units like RTN, fp32-scale numerics
+    const bool w8 = mode & 8; // int8-weight formats: 1024 B per (16-channel group, 64-k block), no scale / zero-point rows in the stage
+    const bool fixed = mode & 1, rtn = (mode & 2) || (mode & 4) || w8; // bit 2 (peer-store epilogue): 128-k units like RTN, fp32-scale numerics
     if(M < 1 || M > 32) return set_error(CKB_ERR_UNSUPPORTED, "W4 decode kernel handles 1 <= M <= 32 per launch");
     s.nt = M <= 8 ? 1 : (M <= 16 ? 2 : 4);
     s.rb = s.nt == 1 ? (M <= 1 ? 1 : (M <= 2 ? 2 : (M <= 4 ? 4 : 8))) : 8 * s.nt;
@@ -86,9 +87,9 @@ int schedule_wq_gemv2(int M, int N, int K, bool zp, int sms, G2Sched& s, int mod
             const int chk    = wk * upw * kbu, rows = chk / 2;
             if(chk > 256 || (upw > 1 && wk * (upw / 2) * kbu >= s.kb_total)) continue; // TMA box limit; no point in empty units
             const int a_b    = al(chk * s.rb * 128, 1024);
-            const int w_b    = g_alloc * chk * 512;
-            const int s_b    = al(rows * 32 * g_alloc + 64, 128);
-            const int z_b    = zp ? al(rows * 16 * g_alloc + 64, 128) : 0;
+            const int w_b    = g_alloc * chk * (w8 ? 1024 : 512);
+            const int s_b    = w8 ? 0 : al(rows * 32 * g_alloc + 64, 128);
+            const int z_b    = (zp && !w8) ? al(rows * 16 * g_alloc + 64, 128) : 0;
             const int stage  = al(a_b + w_b + s_b + z_b, 1024);
             const int chunks = (s.kb_total + chk - 1) / chk;
             const int steps  = s.passes * chunks;
@@ -110,8 +111,8 @@ int schedule_wq_gemv2(int M, int N, int K, bool zp, int sms, G2Sched& s, int mod
     const int chk = wk * s.upw * s.kbu, rows = chk / 2;
     s.n_chunks = (s.kb_total + chk - 1) / chk;
     s.off_w    = al(chk * s.rb * 128, 1024);
-    s.off_s    = s.off_w + g_alloc * chk * 512;
-    s.off_z    = s.off_s + al(rows * 32 * g_alloc + 64, 128);
+    s.off_s    = s.off_w + g_alloc * chk * (w8 ? 1024 : 512);
+    s.off_z    = s.off_s + (w8 ? 0 : al(rows * 32 * g_alloc + 64, 128));
     int end    = s.ring * s.stage_bytes;
     if(s.passes > 1) { s.red_off = end; end += red_bytes; }
     else s.red_off = 0;
@@ -128,13 +129,15 @@ int plan_wq_gemv2(const ckb_gemm_problem& p, ckb_gemm_plan& plan)
     const bool zp  = p.zero != nullptr;
     const int sms  = device_info().sm_count > 0 ? device_info().sm_count : 148;
     G2Sched s{};
-    const int mode = ((p.flags & CKB_FLAG_FIXED_K_ORDER) ? 1 : 0) | (p.b_op == CKB_BOP_GROUP_RTN ? 2 : 0) | (p.num_peers > 0 ? 4 : 0);
+    const bool w8  = p.b_op != CKB_BOP_GROUP && p.b_op != CKB_BOP_GROUP_RTN;
+    const int mode = ((p.flags & CKB_FLAG_FIXED_K_ORDER) ? 1 : 0) | (p.b_op == CKB_BOP_GROUP_RTN ? 2 : 0) | (p.num_peers > 0 ? 4 : 0) | (w8 ? 8 : 0);
     if(int rc = schedule_wq_gemv2(p.M, p.N, p.K, zp, sms, s, mode)) return rc;
     gp->nt = s.nt; gp->gw = s.gw; gp->passes = s.passes; gp->slot_q = s.slot_q; gp->slot_r = s.slot_r; gp->g_hi = s.g_hi;
     gp->wn_log2 = s.wn_log2; gp->kbu = s.kbu; gp->upw = s.upw; gp->n_chunks = s.n_chunks; gp->ring = s.ring; gp->stage_bytes = s.stage_bytes;
     gp->off_w = s.off_w; gp->off_s = s.off_s; gp->off_z = s.off_z;
     gp->red_off = s.red_off; gp->bar_off = s.bar_off; gp->smem_bytes = s.smem_bytes; gp->rb = s.rb;
     gp->rtn = (mode & 2) ? 1 : 0;
+    gp->wf  = !w8 ? 0 : (p.b_op == CKB_BOP_MULTIPLY ? 1 : (p.b_op == CKB_BOP_FPAINTB ? 2 : 3));
 
     const int chk = (g2_warps(s.nt) >> s.wn_log2) * s.upw * s.kbu;
     const CUtensorMapDataType adt = f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
@@ -146,7 +149,19 @@ int plan_wq_gemv2(const ckb_gemm_problem& p, ckb_gemm_plan& plan)
                                    s.rb >= 4 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE)) return rc;
     }
     const int kg_total = (p.K + 127) / 128;
-    for(int i = 0; i < 2; ++i)
+    for(int i = 0; i < 2 && w8; ++i)
+    {
+        // int8 weights B[n][k] (K-major, pitch ldb) viewed as (64 B, N rows, K/64 blocks): a box lands as [k-block][row][64 B], so the
+        // eight rows a quarter-warp reads are contiguous (conflict-free LDS.128)
+        const int gb = i == 0 ? s.g_hi : std::max(1, s.g_hi - 1);
+        const uint64_t dims[3] = {64, uint64_t(p.N), uint64_t(s.kb_total)};
+        const uint64_t str[2]  = {uint64_t(p.ldb), 64};
+        const uint32_t box[3]  = {64, uint32_t(16 * gb), uint32_t(chk)};
+        if(int rc = encode_tmap_nd(&gp->tmW[i], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, p.b, dims, str, box, CU_TENSOR_MAP_SWIZZLE_NONE)) return rc;
+        gp->tmS[i] = gp->tmW[i];
+        gp->tmZ[i] = gp->tmW[i];
+    }
+    for(int i = 0; i < 2 && !w8; ++i)
     {
         const int gb = i == 0 ? s.g_hi : std::max(1, s.g_hi - 1);
         {   // packed weights [n16 group][k64 block][128 words]
@@ -176,7 +191,8 @@ int plan_wq_gemv2(const ckb_gemm_problem& p, ckb_gemm_plan& plan)
     plan.smem_bytes      = gp->smem_bytes;
     plan.split_units     = 1;
     plan.workspace_bytes = 0;
-    snprintf(plan.kernel_name, sizeof plan.kernel_name, "wq_gemv2_w4g128%s_%s_hmma_%dx%dwarps_g%d_p%d_m%d_u%dx%d_r%d%s", (mode & 2) ? "rtn" : "",
+    static const char* wfn[] = {"w4g128", "w8mul", "w8fpaintb", "w8pass"};
+    snprintf(plan.kernel_name, sizeof plan.kernel_name, "wq_gemv2_%s%s_%s_hmma_%dx%dwarps_g%d_p%d_m%d_u%dx%d_r%d%s", wfn[gp->wf], (mode & 2) ? "rtn" : "",
              f16 ? "f16" : "bf16", 1 << s.wn_log2, g2_warps(s.nt) >> s.wn_log2, s.gw, s.passes, 8 * s.nt, s.upw, s.kbu, s.ring,
              (mode & 1) ? "_korder" : "");
     return CKB_OK;
@@ -231,6 +247,8 @@ int run_wq_gemv2(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStrea
     a.zero_const = p.zero_const;
     a.has_zero   = p.zero != nullptr;
     a.rtn        = gp->rtn;
+    a.wf         = gp->wf;
+    a.ch_scale   = static_cast<const uint16_t*>(p.scale);
     // the optional paths live in the EXT instantiation (128-k units, fp32-scale numerics): peers force it through the schedule
     // (mode bit 2), the inputs-ready hint is honoured when the plan happens to use 128-k units and is ignored otherwise
     a.nodep      = ((p.flags & CKB_FLAG_INPUTS_READY) && gp->kbu == 2 && !gp->rtn) ? 1 : 0;

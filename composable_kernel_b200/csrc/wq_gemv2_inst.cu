@@ -16,6 +16,25 @@ int GV_FN(int nt, int gw, int kbu, const G2Plan* gp, const G2Args& a, int grid, 
 {
     constexpr bool F16 = GV_INST_F16 != 0;
     const bool zp      = a.has_zero != 0;
+    if(a.wf != 0)
+    {
+        // int8-weight formats (K-major int8 streamed by TMA): Multiply / PassThrough for bf16 A, fpAintB / PassThrough for fp16 A
+#define GV_CASE8(NT_, GW_)                                                                                                   \
+    if(nt == NT_ && gw == GW_)                                                                                               \
+    {                                                                                                                        \
+        if(a.wf == 3) return launch_gemv2<NT_, GW_, 2, F16, false, false, false, 3>(gp, a, grid, st);                       \
+        return launch_gemv2<NT_, GW_, 2, F16, false, false, false, (F16 ? 2 : 1)>(gp, a, grid, st);                          \
+    }
+#if GV_INST_NT == 1
+        GV_CASE8(1, 1) GV_CASE8(1, 2) GV_CASE8(1, 3) GV_CASE8(1, 4)
+#elif GV_INST_NT == 2
+        GV_CASE8(2, 1) GV_CASE8(2, 2) GV_CASE8(2, 3) GV_CASE8(2, 4)
+#else
+        GV_CASE8(4, 1) GV_CASE8(4, 2)
+#endif
+#undef GV_CASE8
+        return set_error(CKB_ERR_INVALID, "no W8 decode kernel variant for nt %d gw %d", nt, gw);
+    }
 #define GV_CASE(NT_, GW_)                                                                                                    \
     if(nt == NT_ && gw == GW_)                                                                                               \
     {                                                                                                                        \

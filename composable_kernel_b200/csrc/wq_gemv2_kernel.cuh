@@ -54,6 +54,9 @@ struct G2Args
     int zero_const;
     int has_zero;
     int pdl;        // launch with programmatic stream serialization
+    int wf;         // weight format: 0 = packed int4 group-128 (W4A16); 1 = int8 x per-channel bf16 scale (Multiply), 2 = biased uint8 x
+                    // fp16 scale (fpAintB), 3 = int8 PassThrough -- K-major int8 streamed as [kb][row][64 B] boxes (W8 instantiations)
+    const uint16_t* ch_scale; // W8 formats 1, 2: per-channel scale [N] in A's type
     int ext;        // launch the EXT instantiation (peers or nodep requested; 128-k units, fp32-scale numerics)
     int nodep;      // CKB_FLAG_INPUTS_READY (EXT instantiation): do not wait for the previous grid before reading A; wait before exit
     int rtn;        // CKB_BOP_GROUP_RTN: (q - zp) * s rounded once into A's type before the MMA (RTN kernel instantiation)
@@ -111,7 +114,7 @@ static __device__ __noinline__ void g2_store_peers(const EpiParams& ep, int m, i
 // EXT = the instantiation with the optional paths compiled in (peer-store epilogue of the fused all-gather, CKB_FLAG_INPUTS_READY):
 // the kernel is so sensitive to its dynamic instruction count that even never-taken branches cost 2-5 % (A/B against the build
 // without them, profiles/r2_gemv_ab_ext.txt), so the default instantiation does not contain them.
-template <int NT, int GW, int KBU, bool F16, bool ZP, bool RTN, bool EXT>
+template <int NT, int GW, int KBU, bool F16, bool ZP, bool RTN, bool EXT, int WF = 0>
 __global__ void __launch_bounds__(g2_threads(NT), 2)
 wq_gemv2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW0,
                 const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ CUtensorMap tmS0,
@@ -170,6 +173,13 @@ wq_gemv2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         const uint32_t bar = full_bar(s);
         const bool hi      = (sg == args.g_hi);
         const int rows     = (CHK + 1) >> 1; // scale rows per stage
+        if(WF != 0)
+        {
+            // int8 weights, K-major in HBM: one box of [CHK k-blocks][16 sg rows][64 B] (per-channel scales are read once per pass)
+            ptx::mbar_arrive_expect_tx(bar, CHK * RB * 128u + sg * CHK * 1024u);
+            ptx::tma_load_3d_hint(st + args.off_w, hi ? &tmW0 : &tmW1, bar, 0, sb * 16, c * CHK, pol_stream);
+            return;
+        }
         uint32_t bytes     = CHK * RB * 128u + sg * (CHK * 512u + rows * 32u);
         if(ZP) bytes += sg * rows * 16u;
         ptx::mbar_arrive_expect_tx(bar, bytes);
@@ -244,6 +254,19 @@ wq_gemv2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 #pragma unroll
                 for(int e = 0; e < 4; ++e) acc[gi][nt][e] = 0.f;
         const uint32_t w_g0 = w_off + g0 * (CHK * 512);
+        // W8 formats: the per-channel scales of this lane's two rows (g, g + 8) of each group, packed lo | hi << 16 in A's type
+        uint32_t sc8[GW];
+        if(WF == 1 || WF == 2)
+        {
+#pragma unroll
+            for(int gi = 0; gi < GW; ++gi)
+            {
+                const int n_lo = 16 * (sb + g0 + gi) + g;
+                const uint32_t lo = (gi < G && n_lo < args.N) ? args.ch_scale[n_lo] : 0u;
+                const uint32_t hi = (gi < G && n_lo + 8 < args.N) ? args.ch_scale[n_lo + 8] : 0u;
+                sc8[gi] = lo | (hi << 16);
+            }
+        }
         const uint32_t s_g0 = args.off_s + (g0 * 16 + g) * 2;
         const uint32_t z_g0 = args.off_z + g0 * 16 + g;
 
@@ -295,6 +318,44 @@ wq_gemv2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 for(int gi = 0; gi < GW; ++gi)
                 {
                     if(GW > 1 && gi == GW - 1 && G < GW) break;
+                    if(WF != 0)
+                    {
+                        // int8 weights: rows g and g + 8 of the group, 16 bytes = the lane's k slice of the 64-k block (k = 16 t + 4 ks + i,
+                        // the same permutation the activation fragments use); dequantised with the reference functor's arithmetic and
+                        // multiplied straight into the accumulators
+                        const uint32_t row_b = st + args.off_w + (uint32_t(g0 + gi) * 16u + uint32_t(g)) * 64u + uint32_t(t) * 16u;
+                        const uint32_t kb_st = uint32_t(sg) * 1024u; // bytes of one k-block of the slot's rows
+                        const uint32_t s2_lo = (sc8[gi] & 0xFFFFu) * 0x10001u, s2_hi = (sc8[gi] >> 16) * 0x10001u; // fp16 pairs
+#pragma unroll
+                        for(int b = 0; b < KBU; ++b)
+                        {
+                            const uint32_t ad  = row_b + uint32_t(kb_u + b) * kb_st;
+                            const uint4 lo4    = ptx::lds128(ad), hi4 = ptx::lds128(ad + 512);
+                            const uint32_t lw[4] = {lo4.x, lo4.y, lo4.z, lo4.w}, hw[4] = {hi4.x, hi4.y, hi4.z, hi4.w};
+#pragma unroll
+                            for(int ks = 0; ks < 4; ++ks)
+                            {
+                                uint32_t ol[2], oh[2];
+                                if(WF == 2) { dequant_u8x4_fpaintb(lw[ks], s2_lo, ol); dequant_u8x4_fpaintb(hw[ks], s2_hi, oh); }
+                                else if(WF == 1)
+                                {
+                                    dequant_s8x4_mul_bf16(lw[ks], __uint_as_float(sc8[gi] << 16), ol);
+                                    dequant_s8x4_mul_bf16(hw[ks], __uint_as_float(sc8[gi] & 0xFFFF0000u), oh);
+                                }
+                                else { dequant_s8x4_pass<F16>(lw[ks], ol); dequant_s8x4_pass<F16>(hw[ks], oh); }
+                                const uint32_t a[4] = {ol[0], oh[0], ol[1], oh[1]};
+#pragma unroll
+                                for(int nt = 0; nt < NT; ++nt)
+                                {
+                                    const uint4 bb = bf[b][nt][ks >> 1];
+                                    if(ks & 1) ptx::mma_m16n8k16<F16>(acc[gi][nt], a, bb.z, bb.w);
+                                    else ptx::mma_m16n8k16<F16>(acc[gi][nt], a, bb.x, bb.y);
+                                }
+                            }
+                        }
+                        (void)s2_lo; (void)s2_hi;
+                        continue;
+                    }
                     const uint32_t sl = ptx::lds_u16(s_u + gi * 32), sh = ptx::lds_u16(s_u + gi * 32 + 16);
                     uint32_t zm_lo, zm_hi; // magic + zero point of the two channel rows (one 16-bit value; doubled for the exact path)
                     if(ZP)
@@ -460,16 +521,16 @@ struct G2Plan
 {
     CUtensorMap tmA, tmW[2], tmS[2], tmZ[2];
     int32_t nt, gw, passes, slot_q, slot_r, g_hi, wn_log2, kbu, upw, n_chunks, ring, stage_bytes, off_w, off_s, off_z, red_off, bar_off,
-        smem_bytes, rb, rtn;
+        smem_bytes, rb, rtn, wf;
 };
 
 // per-(dtype, NT) launchers: each lives in its own translation unit (wq_gemv2_inst.cu, -DGV_INST_F16 / -DGV_INST_NT)
 int launch_gemv2_variant(bool f16, int nt, int gw, int kbu, const G2Plan* gp, const G2Args& a, int grid, cudaStream_t stream);
 
-template <int NT, int GW, int KBU, bool F16, bool ZP, bool RTN, bool EXT>
+template <int NT, int GW, int KBU, bool F16, bool ZP, bool RTN, bool EXT, int WF = 0>
 static int launch_gemv2(const G2Plan* gp, const G2Args& a, int grid, cudaStream_t stream)
 {
-    auto kfn = wq_gemv2_kernel<NT, GW, KBU, F16, ZP, RTN, EXT>;
+    auto kfn = wq_gemv2_kernel<NT, GW, KBU, F16, ZP, RTN, EXT, WF>;
     // the opt-in is per device (cudaFuncSetAttribute applies to the current device only): one flag per device ordinal
     static unsigned long long attr_mask = 0;
     int dev = 0;

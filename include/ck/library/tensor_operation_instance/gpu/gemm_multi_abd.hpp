@@ -78,6 +78,11 @@ struct DeviceOperationInstanceFactory<
             op_ptrs.push_back(std::make_unique<DeviceGemmMultipleABD_Sm100<AsLayout, BsLayout, DsLayout, ELayout, AsDataType, BsDataType, F32, F32,
                                                                            DsDataType, EDataType, AOp, BOp, CDEOp, GemmSpecialization::Default,
                                                                            CKB_FLAG_PREFILL_TWO_PASS>>());
+            // third instance: decode rows (M <= 64) on the stream-K tcgen05 kernel (weights as the TMEM A operand) instead of the
+            // N-split HMMA kernel
+            op_ptrs.push_back(std::make_unique<DeviceGemmMultipleABD_Sm100<AsLayout, BsLayout, DsLayout, ELayout, AsDataType, BsDataType, F32, F32,
+                                                                           DsDataType, EDataType, AOp, BOp, CDEOp, GemmSpecialization::Default,
+                                                                           CKB_FLAG_W8_STREAMK>>());
         }
         return op_ptrs;
     }

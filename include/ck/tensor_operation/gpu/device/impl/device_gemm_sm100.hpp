@@ -48,7 +48,7 @@ inline std::string type_string(const char* cls, const GemmArgument* a = nullptr)
 // null-safe downcast of the type-erased argument (the reference dereferences dynamic_cast unchecked)
 inline const char* flags_tag(uint32_t f)
 {
-    return (f & CKB_FLAG_SS_1CTA) ? "[1cta]" : (f & CKB_FLAG_SS_2CTA) ? "[2cta]" : (f & CKB_FLAG_PREFILL_TWO_PASS) ? "[two_pass]" : (f & CKB_FLAG_GEMV_SINGLE_PRODUCER) ? "[single_producer]" : "";
+    return (f & CKB_FLAG_SS_1CTA) ? "[1cta]" : (f & CKB_FLAG_SS_2CTA) ? "[2cta]" : (f & CKB_FLAG_PREFILL_TWO_PASS) ? "[two_pass]" : (f & CKB_FLAG_GEMV_SINGLE_PRODUCER) ? "[single_producer]" : (f & CKB_FLAG_W8_STREAMK) ? "[stream_k]" : "";
 }
 inline const GemmArgument& checked(const BaseArgument* p)
 {

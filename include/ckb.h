@@ -109,6 +109,7 @@ enum {
     CKB_FLAG_SS_2CTA   = 1 << 3,            /* ... CTA pair (cta_group::2) per 256x256 tile */
     CKB_FLAG_PREFILL_TWO_PASS = 1 << 4,     /* weight-quantized prefill: dequant pass into workspace + dense GEMM (round-1 form) */
     CKB_FLAG_GEMV_SINGLE_PRODUCER = 1 << 5, /* W4A16 decode: single-producer kernel (wq_gemv) instead of the rotating-producer one */
+    CKB_FLAG_W8_STREAMK = 1 << 7,           /* int8-weight decode rows: the stream-K tcgen05 kernel (TMEM A operand) instead of the HMMA one */
     CKB_FLAG_INPUTS_READY = 1 << 6          /* [EXT] the caller asserts that A, D and the weights of THIS GEMM are not written by the
                                                kernel launched just before it on the stream (e.g. the k / v projections after q, `up` after
                                                `gate`: same layer input).  Under programmatic dependent launch (graph replay) the W4A16 decode

@@ -38,7 +38,7 @@ def run_w4a16(a, q_kn, s, z=None, zero_const=8, f16=False, out_f32=False, ds=(),
     return (e.cpu().numpy() if f16 else from_dev_bf16(e)), op
 
 
-def run_w8a16_bf16(a, qn, s, bias, cde, b_op="mul"):
+def run_w8a16_bf16(a, qn, s, bias, cde, b_op="mul", flags=0):
     """a bf16 bits [M,K]; qn int8 [N,K] (column-major B); s, bias bf16 bits [N]."""
     import torch
     from composable_kernel_b200 import capi, ops
@@ -49,7 +49,7 @@ def run_w8a16_bf16(a, qn, s, bias, cde, b_op="mul"):
               "add_gelu": capi.CDE_ADD_FASTGELU}[cde]
     ds = (to_dev(bias, True),) if "add" in cde else ()
     op = ops.GemmOp(to_dev(a, True), to_dev(qn), e, b_op=capi.BOP_MULTIPLY if b_op == "mul" else capi.BOP_PASSTHROUGH,
-                    scale=to_dev(s, True) if b_op == "mul" else None, ds=ds, d_strides=((0, 1),) * len(ds), cde_op=cde_op)
+                    scale=to_dev(s, True) if b_op == "mul" else None, ds=ds, d_strides=((0, 1),) * len(ds), cde_op=cde_op, flags=flags)
     assert op.supported, op.why
     op.run()
     torch.cuda.synchronize()

@@ -1,4 +1,4 @@
-python -m pytest tests -m gpu -x -q > gpurun_out/s4_pytest.log 2>&1; tail -3 gpurun_out/s4_pytest.log
-python -c "import __graft_entry__ as g; g.smoke()"
-python bench.py > gpurun_out/s4_bench.json 2> gpurun_out/s4_bench.err; echo bench rc=$?
-python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/s4_bench_ref.json 2> gpurun_out/s4_bench_ref.err; echo ref rc=$?; tail -c 600 gpurun_out/s4_bench_ref.json
+python -m pytest tests -m gpu -x -q 2>&1 | tail -4
+tests/profiler/bin/ckProfiler gemm_multi_abd 0 1 1 0 2 0 1 16 11008 4096 -1 -1 -1 | grep "^Perf\|^Best\|found"
+tests/profiler/bin/ckProfiler fpAintB_gemm 0 2 0 1 16 11008 4096 | grep "^Perf"
+tests/profiler/bin/ckProfiler gemm_universal_reduce 0 0 0 2 0 1 16 4096 4096 -1 -1 -1 4 | grep "^Perf"

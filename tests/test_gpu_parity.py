@@ -467,3 +467,25 @@ def test_torch_custom_ops_match_the_oracle():
     refe = o.gemm(ai, o.I8, bn.T, o.I8, o.BF16, cshuffle_dtype=o.I32, ds=(np.broadcast_to(d0, (64, 128)), np.broadcast_to(d1[:, None], (64, 128))),
                   d_dtypes=(o.F32, o.F32), cde_op=o.CDE_MULTIPLY_MULTIPLY)
     assert np.array_equal(H.from_dev_bf16(e), refe)
+
+
+@pytest.mark.parametrize("M,N,K,cde", [(8, 256, 512, "add"), (16, 4096, 4096, "pass"), (33, 384, 640, "add_gelu"), (1, 11008, 4096, "add")])
+def test_w8a16_decode_both_kernels_vs_oracle(M, N, K, cde):
+    """int8-weight decode rows on the N-split HMMA kernel (default) and on the stream-K tcgen05 kernel (CKB_FLAG_W8_STREAMK,
+    the second factory instance): same oracle, same tolerance"""
+    from composable_kernel_b200 import capi
+    o = orc()
+    rng = np.random.default_rng(M * 3 + N + K)
+    a = rand_bf16(rng, (M, K))
+    qn = rng.integers(-128, 128, (N, K), dtype=np.int8)
+    s = o.bf16_trunc((rng.random(N) * 0.02 + 0.001).astype(np.float32))
+    bias = rand_bf16(rng, (N,))
+    op_id = {"pass": o.CDE_PASSTHROUGH, "add": o.CDE_ADD, "gelu": o.CDE_FASTGELU, "add_gelu": o.CDE_ADD_FASTGELU}[cde]
+    ds = (np.broadcast_to(bias, (M, N)),) if "add" in cde else ()
+    ref = o.gemm(a, o.BF16, qn.T, o.I8, o.BF16, b_op=o.BOP_MULTIPLY, scale=np.broadcast_to(s, (K, N)), s_dtype=o.BF16,
+                 ds=ds, d_dtypes=(o.BF16,) * len(ds), cde_op=op_id)
+    for flags, tag in ((0, "wq_gemv2_w8mul"), (capi.FLAG_W8_STREAMK, "streamk")):
+        got, op = H.run_w8a16_bf16(a, qn, s, bias, cde, flags=flags)
+        assert tag in op.kernel_name, op.kernel_name
+        bad, err = H.bf16_close(got, ref, RTOL, ATOL)
+        assert bad == 0, f"{op.kernel_name}: max err {err}"
