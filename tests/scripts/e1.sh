@@ -1,4 +1,3 @@
-python -m pytest tests -m gpu -x -q 2>&1 | tail -4
-tests/profiler/bin/ckProfiler gemm_multi_abd 0 1 1 0 2 0 1 16 11008 4096 -1 -1 -1 | grep "^Perf\|^Best\|found"
-tests/profiler/bin/ckProfiler fpAintB_gemm 0 2 0 1 16 11008 4096 | grep "^Perf"
-tests/profiler/bin/ckProfiler gemm_universal_reduce 0 0 0 2 0 1 16 4096 4096 -1 -1 -1 4 | grep "^Perf"
+python -m pytest tests/test_gpu_shard.py -m gpu -q -x 2>&1 | tail -3
+python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29516 bench.py --gpus 8 --steps 10 --warmup 3 > gpurun_out/s4_bench_n8.json 2> gpurun_out/s4_bench_n8.err; echo rc=$?
+head -c 300 gpurun_out/s4_bench_n8.json
