@@ -1,3 +1,5 @@
-python -m pytest tests/test_gpu_shard.py -m gpu -q -x 2>&1 | tail -3
-python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29516 bench.py --gpus 8 --steps 10 --warmup 3 > gpurun_out/s4_bench_n8.json 2> gpurun_out/s4_bench_n8.err; echo rc=$?
-head -c 300 gpurun_out/s4_bench_n8.json
+python -m pytest tests/test_gpu_parity.py -m gpu -q -x -k "chain or w4 or golden" 2>&1 | tail -5
+export PERF_GRAPH=1
+S="w4 1 4096 4096 w4 1 11008 4096 w4 1 4096 11008 w4 4 4096 4096 w4 16 4096 4096"
+echo "== hardware PDL chain"; python tests/perf_probe.py $S
+echo "== software dependency chain"; PERF_CHAIN=1 python tests/perf_probe.py $S
