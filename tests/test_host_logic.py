@@ -190,3 +190,18 @@ def test_torch_custom_ops_trace_with_fake_tensors():
         a = torch.empty(64, 256, dtype=torch.int8)
         e = torch.ops.ckb.int8_gemm_scaled(a, torch.empty(128, 256, dtype=torch.int8), torch.empty(128), torch.empty(64))
         assert tuple(e.shape) == (64, 128) and e.dtype == torch.bfloat16
+
+
+# ------------------------------------------------------------------ ASan + UBSan over the oracle and the header-only host layer
+def test_oracle_and_host_layer_under_asan_ubsan():
+    """`make -C oracle sanitize` builds oracle/_san/sanitize_main with -fsanitize=address,undefined (the reference's sanitizer build
+    switch, CMakeLists.txt:111-118): every oracle weight format / epilogue on ragged shapes, strided and broadcast operands, row
+    sampling, threads; Tensor / functors / conversions of include/ck.  Any report aborts the binary (non-zero exit)."""
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run(["make", "-C", os.path.join(root, "oracle"), "sanitize", "-s"], capture_output=True, text=True)
+    if r.returncode != 0:
+        pytest.skip("no sanitizer runtime for the host compiler here: " + r.stderr[-200:])
+    r = subprocess.run([os.path.join(root, "oracle", "_san", "sanitize_main")], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "sanitize_main: OK" in r.stdout, (r.stdout[-1500:], r.stderr[-3000:])
