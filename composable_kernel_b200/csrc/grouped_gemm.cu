@@ -42,6 +42,7 @@ struct GroupedArgs
     GroupedLayout L;
     int G, N, K;
     int has_scale, num_d, d_dtype;
+    int a_col; // A is column-major (km_*): A[m,k] = a[k * StrideA + m]
     int cde_op;
     uint32_t flags;
 };
@@ -132,6 +133,28 @@ __global__ void __launch_bounds__(GG_THREADS, 2) grouped_gemm_kernel(const Group
         uint4 ra[4], rb[2];
         auto load_regs = [&](int kt) {
             const int k0 = kt * GG_BK;
+            if(ga.a_col)
+            {
+                // column-major A: vectors run along m (8 rows at one k); 16-byte loads when the pitch and the pointer allow it,
+                // element loads otherwise and at the ragged end of the group (rows past M_g repeat the last row)
+                const bool vec_ok = (lda % 8 == 0) && ((reinterpret_cast<uintptr_t>(A) & 15) == 0);
+#pragma unroll
+                for(int i = 0; i < 4; ++i)
+                {
+                    const int c = tid + i * GG_THREADS, k = c >> 3, mc = (c & 7) * 8;
+                    if(k0 + k >= ga.K) { ra[i] = make_uint4(0, 0, 0, 0); continue; }
+                    const uint16_t* col = A + (long long)(k0 + k) * lda;
+                    if(vec_ok && m0 + mc + 8 <= Mg) ra[i] = *reinterpret_cast<const uint4*>(col + m0 + mc);
+                    else
+                    {
+                        uint16_t e[8];
+#pragma unroll
+                        for(int j = 0; j < 8; ++j) e[j] = col[min(m0 + mc + j, Mg - 1)];
+                        ra[i] = make_uint4(e[0] | uint32_t(e[1]) << 16, e[2] | uint32_t(e[3]) << 16, e[4] | uint32_t(e[5]) << 16, e[6] | uint32_t(e[7]) << 16);
+                    }
+                }
+            }
+            else
 #pragma unroll
             for(int i = 0; i < 4; ++i)
             {
@@ -159,6 +182,19 @@ __global__ void __launch_bounds__(GG_THREADS, 2) grouped_gemm_kernel(const Group
         auto store_smem = [&](int b) {
             uint16_t* As = As_base + b * GG_A_ELEMS;
             uint16_t* Bs = Bs_base + b * GG_B_ELEMS;
+            if(ga.a_col)
+            {
+                // transpose on the way in: the register holds 8 rows at one k
+#pragma unroll
+                for(int i = 0; i < 4; ++i)
+                {
+                    const int c = tid + i * GG_THREADS, k = c >> 3, mc = (c & 7) * 8;
+                    const uint32_t w[4] = {ra[i].x, ra[i].y, ra[i].z, ra[i].w};
+#pragma unroll
+                    for(int j = 0; j < 8; ++j) As[(mc + j) * GG_PITCH_K + k] = uint16_t(w[j >> 1] >> (16 * (j & 1)));
+                }
+            }
+            else
 #pragma unroll
             for(int i = 0; i < 4; ++i)
             {
@@ -341,7 +377,7 @@ int check_grouped(const ckb_gemm_problem& p, int group_count)
 {
     if(group_count <= 0) return set_error(CKB_ERR_UNSUPPORTED, "group_count must be positive");
     if(p.a_dtype != CKB_BF16 || p.e_dtype != CKB_BF16) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: A and E must be bf16");
-    if(p.a_layout != CKB_ROW) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: A must be row-major (km_* is not built)");
+    if(p.a_layout != CKB_ROW && p.a_layout != CKB_COL) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: A must be row- or column-major");
     if(p.b_dtype != CKB_I8) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: B0 must be int8");
     if(p.b_layout != CKB_ROW && p.b_layout != CKB_COL) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: B0 must be row- or column-major");
     if(p.b_op != CKB_BOP_MULTIPLY && p.b_op != CKB_BOP_PASSTHROUGH) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: B op must be Multiply or PassThrough");
@@ -359,7 +395,8 @@ int check_grouped(const ckb_gemm_problem& p, int group_count)
     }
     if(p.N <= 0 || p.K <= 0) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: N and K must be positive");
     if(p.K % 16 || p.N % 16) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: N and K must be multiples of 16");
-    if(p.lda % 8 || p.lda < p.K) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: StrideA must be >= K and a multiple of 8");
+    if(p.a_layout == CKB_ROW && (p.lda % 8 || p.lda < p.K)) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: StrideA must be >= K and a multiple of 8");
+    if(p.a_layout == CKB_COL && p.lda < 1) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: StrideA (pitch between k rows of column-major A) must be >= M");
     const int b_inner = p.b_layout == CKB_ROW ? p.N : p.K;
     if(p.ldb % 16 || p.ldb < b_inner) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: StrideB0 must cover the row and be a multiple of 16");
     if(p.lde % 2 || p.lde < p.N) return set_error(CKB_ERR_UNSUPPORTED, "grouped GEMM: StrideE must be >= N and even");
@@ -378,6 +415,7 @@ int run_grouped(const ckb_gemm_problem& p, const void* dev_args, int group_count
     ga.G = group_count; ga.N = p.N; ga.K = p.K;
     ga.has_scale = num_b == 2; ga.num_d = p.num_d; ga.d_dtype = p.d_dtype[0];
     ga.cde_op = p.cde_op; ga.flags = p.flags;
+    ga.a_col  = p.a_layout == CKB_COL;
     const long long NT    = (p.N + GG_BN - 1) / GG_BN;
     const long long tiles = ((long long)(sum_m + GG_BM - 1) / GG_BM + group_count) * NT; // upper bound on the tile count
     const int grid        = int(std::min<long long>(tiles, 3LL * device_info().sm_count));

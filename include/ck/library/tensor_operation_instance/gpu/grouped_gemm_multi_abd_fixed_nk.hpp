@@ -2,7 +2,7 @@
 // entry points and the factory of library/include/ck/library/tensor_operation_instance/gpu/
 // grouped_gemm_multi_abd_fixed_nk.hpp:25-470.  The reference registers 10 tile-shape instantiations per entry point
 // (.../grouped_gemm_fixed_nk_multi_abd/..._mk_kn_mn_common.hpp); here each registers ONE sm_100a operator.
-// km_kn_mn (column-major A) entry points exist and register an operator whose IsSupportedArgument is false.
+// All three layouts of the reference are served: mk_kn_mn, mk_nk_mn and km_kn_mn (column-major A: transposed on the way into shared memory).
 #pragma once
 #include "ck/library/tensor_operation_instance/device_operation_instance_factory.hpp"
 #include "ck/tensor_operation/gpu/device/impl/device_grouped_gemm_multi_abd_xdl_fixed_nk.hpp"

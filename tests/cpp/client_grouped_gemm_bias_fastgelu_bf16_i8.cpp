@@ -19,8 +19,8 @@ using PassThrough = ck::tensor_operation::element_wise::PassThrough;
 using Multiply = ck::tensor_operation::element_wise::Multiply;
 using AddFastGelu = ck::tensor_operation::element_wise::AddFastGelu;
 
-template <typename BLayout>
-int run(int group_count, ck::index_t N, ck::index_t K, bool verify)
+template <typename BLayout, typename ALayout = Row>
+int run(int group_count, ck::index_t N, ck::index_t K, bool verify, ck::index_t a_pitch = 64)
 {
     using namespace ck::literals;
     constexpr bool b_row = std::is_same_v<BLayout, Row>;
@@ -34,11 +34,14 @@ int run(int group_count, ck::index_t N, ck::index_t K, bool verify)
     std::vector<std::unique_ptr<DeviceMem>> a0_buf, b0_buf, b1_buf, d0_buf, e_buf;
     std::vector<ck::tensor_operation::device::GemmMultiABDDesc> gemm_descs;
     std::vector<ck::tensor_operation::device::GroupedGemmMultiABDKernelArgument<NumATensor, NumBTensor, NumDTensor>> kargs;
-    const ck::index_t StrideA = K, StrideB = b_row ? N : K, StrideE = N;
+    constexpr bool a_row = std::is_same_v<ALayout, Row>;
+    // km_kn_mn: A[m,k] = a[k * StrideA + m]; one pitch >= max M for every group (64: 16-byte vector loads; 67: the element path)
+    const ck::index_t StrideA = a_row ? K : a_pitch, StrideB = b_row ? N : K, StrideE = N;
     for(int i = 0; i < group_count; ++i)
     {
         const std::size_t M = Ms[i];
-        a0.emplace_back(HostTensorDescriptor({M, std::size_t(K)}, {std::size_t(StrideA), 1_uz}));
+        a0.emplace_back(a_row ? HostTensorDescriptor({M, std::size_t(K)}, {std::size_t(StrideA), 1_uz})
+                              : HostTensorDescriptor({M, std::size_t(K)}, {1_uz, std::size_t(StrideA)}));
         b0.emplace_back(b_row ? HostTensorDescriptor({std::size_t(K), std::size_t(N)}, {std::size_t(StrideB), 1_uz})
                               : HostTensorDescriptor({std::size_t(K), std::size_t(N)}, {1_uz, std::size_t(StrideB)}));
         b1.emplace_back(HostTensorDescriptor({std::size_t(K), std::size_t(N)}, {0_uz, 1_uz}));
@@ -65,7 +68,7 @@ int run(int group_count, ck::index_t N, ck::index_t K, bool verify)
                          std::array<ck::index_t, 1>{StrideA}, std::array<ck::index_t, 2>{StrideB, 0}, std::array<ck::index_t, 1>{0}, StrideE});
     }
 
-    using DeviceOp = ck::tensor_operation::device::DeviceGroupedGemmMultiABDFixedNK<ck::Tuple<Row>, ck::Tuple<BLayout, BLayout>, ck::Tuple<Row>,
+    using DeviceOp = ck::tensor_operation::device::DeviceGroupedGemmMultiABDFixedNK<ck::Tuple<ALayout>, ck::Tuple<BLayout, BLayout>, ck::Tuple<Row>,
                                                                                     Row, ck::Tuple<BF16>, ck::Tuple<I8, BF16>, ck::Tuple<BF16>,
                                                                                     BF16, PassThrough, Multiply, AddFastGelu>;
     const auto op_ptrs = ck::tensor_operation::device::instance::DeviceOperationInstanceFactory<DeviceOp>::GetInstances();
@@ -122,5 +125,6 @@ int main(int argc, char* argv[])
     if(argc >= 4) { groups = std::atoi(argv[1]); N = std::atoi(argv[2]); K = std::atoi(argv[3]); }
     if(argc >= 5) b_col = std::atoi(argv[4]);
     if(argc >= 6) verify = std::atoi(argv[5]);
+    if(argc >= 7 && std::atoi(argv[6]) > 0) return run<Row, Col>(groups, N, K, verify, std::atoi(argv[6]));   // km_kn_mn with this pitch
     return b_col ? run<Col>(groups, N, K, verify) : run<Row>(groups, N, K, verify);
 }

@@ -24,6 +24,8 @@ CASES = [
     ("example_w4a16_group_gemm", ["1", "1024", "512", "0", "0"]),
     ("client_grouped_gemm_bias_fastgelu_bf16_i8", []),                           # client 31: 16 groups, N=1024, K=512, mk_kn_mn
     ("client_grouped_gemm_bias_fastgelu_bf16_i8", ["5", "256", "192", "1", "1"]),  # mk_nk_mn
+    ("client_grouped_gemm_bias_fastgelu_bf16_i8", ["6", "256", "256", "0", "1", "64"]),  # km_kn_mn, pitch 64: vector loads along m
+    ("client_grouped_gemm_bias_fastgelu_bf16_i8", ["5", "128", "192", "0", "1", "67"]),  # km_kn_mn, odd pitch: element loads
     ("client_grouped_gemm_fastgelu_bf16_i8", ["0"]),                             # client 31 FastGelu: KernelArgument<1,2,0> (NumD = 0)
     ("client_grouped_gemm_fastgelu_bf16_i8", ["1"]),                             # client 31 plain: PassThrough, NumD = 0
     ("client_grouped_gemm_fastgelu_bf16_i8", ["0", "5", "256", "192", "1"]),     # NumD = 0, mk_nk_mn
