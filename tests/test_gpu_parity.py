@@ -489,3 +489,30 @@ def test_w8a16_decode_both_kernels_vs_oracle(M, N, K, cde):
         assert tag in op.kernel_name, op.kernel_name
         bad, err = H.bf16_close(got, ref, RTOL, ATOL)
         assert bad == 0, f"{op.kernel_name}: max err {err}"
+
+
+@pytest.mark.parametrize("M,N,K,f16", [(8, 256, 512, True), (16, 1000, 384, True), (4, 512, 1024, False), (40, 264, 256, False), (1, 16, 64, True)])
+def test_int8_passthrough_weight_decode_vs_oracle(M, N, K, f16):
+    """PassThrough<AType, int8_t> B functor at decode sizes (the split-K-reduce family's weight format) for both 16-bit A types"""
+    import torch
+    from composable_kernel_b200 import capi, ops
+    o = orc()
+    rng = np.random.default_rng(M + N + K)
+    qn = rng.integers(-128, 128, (N, K + (-K) % 16), dtype=np.int8)[:, :K]
+    if f16:
+        a = (rng.standard_normal((M, K)) * 0.25).astype(np.float16)
+        ad, e = H.to_dev(a), torch.zeros(M, N, dtype=torch.float16, device="cuda")
+    else:
+        a = rand_bf16(rng, (M, K), 0.25)
+        ad, e = H.to_dev(a, True), torch.zeros(M, N, dtype=torch.bfloat16, device="cuda")
+    op = ops.GemmOp(ad, H.to_dev(np.ascontiguousarray(qn)), e, b_op=capi.BOP_PASSTHROUGH)
+    assert op.supported, op.why
+    op.run()
+    torch.cuda.synchronize()
+    dt = o.F16 if f16 else o.BF16
+    ref = o.gemm(a, dt, qn.T, o.I8, dt, b_op=o.BOP_PASSTHROUGH)
+    if f16:
+        bad, err = H.f_close(e.cpu().numpy(), ref, RTOL, ATOL)
+    else:
+        bad, err = H.bf16_close(H.from_dev_bf16(e), ref, RTOL, ATOL)
+    assert bad == 0, f"{op.kernel_name}: {err}"
