@@ -1,1 +1,4 @@
-python -m pytest tests/test_gpu_parity.py -m gpu -q -x -k "passthrough_weight" 2>&1 | tail -8
+# one GPU call: the whole GPU suite, the smoke test and the default bench line (run under gpurun)
+python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; tail -3 gpurun_out/pytest_gpu.log
+python -c "import __graft_entry__ as g; g.smoke()"
+python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"
