@@ -151,7 +151,10 @@ def test_grouped_argument_layout_and_query_without_gpu():
     p.K = 520
     assert lib.ckb_grouped_gemm_query(C.byref(p), 16) == capi.ERR_UNSUPPORTED and "multiples of 16" in capi.last_error()
     p.K, p.a_layout = 512, capi.COL
-    assert lib.ckb_grouped_gemm_query(C.byref(p), 16) == capi.ERR_UNSUPPORTED   # km_kn_mn is not built
+    p.lda = 64
+    assert lib.ckb_grouped_gemm_query(C.byref(p), 16) == capi.OK                  # km_kn_mn: column-major A, pitch >= M
+    p.a_layout = capi.PREPACKED
+    assert lib.ckb_grouped_gemm_query(C.byref(p), 16) == capi.ERR_UNSUPPORTED
     p.a_layout, p.num_d = capi.ROW, 0
     assert lib.ckb_grouped_gemm_query(C.byref(p), 16) == capi.ERR_UNSUPPORTED   # AddFastGelu needs its D tensor
 
