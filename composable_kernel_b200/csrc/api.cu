@@ -68,6 +68,11 @@ namespace {
 __global__ void __launch_bounds__(256) upload_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, long long n16,
                                                       const unsigned char* src_tail, unsigned char* dst_tail, int tail)
 {
+    // Programmatic dependent launch (used while a stream is being captured): let the GEMM that follows become resident right away
+    // -- it fetches its weights while this copy and the previous GEMM of the stream are still running -- then wait for the
+    // previous GEMM, which may still be reading the staging buffer this copy overwrites.  No-ops in an ordinary launch.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     for(long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (long long)gridDim.x * blockDim.x) dst[i] = src[i];
     if(blockIdx.x == 0 && threadIdx.x < tail) dst_tail[threadIdx.x] = src_tail[threadIdx.x];
 }
@@ -409,9 +414,17 @@ static int run_host_impl(const ckb_gemm_problem* pp, void* staging, void* worksp
     {
         const long long n16 = (long long)(a_bytes / 16);
         const int blocks    = int(std::min<long long>(device_info().sm_count, (n16 + 255) / 256 + 1));
-        upload_kernel<<<blocks, 256, 0, st>>>(static_cast<const uint4*>(src), reinterpret_cast<uint4*>(cur), n16,
-                                              static_cast<const unsigned char*>(src) + n16 * 16, cur + n16 * 16, int(a_bytes % 16));
-        CKB_CUDA_CHECK(cudaGetLastError());
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3(blocks); cfg.blockDim = dim3(256); cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        if(cudaStreamIsCapturing(st, &cs) != cudaSuccess) { cudaGetLastError(); cs = cudaStreamCaptureStatusNone; }
+        cfg.attrs = attr; cfg.numAttrs = cs == cudaStreamCaptureStatusActive ? 1 : 0; // eager PDL launches cost ~20 us of host time
+        CKB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, upload_kernel, static_cast<const uint4*>(src), reinterpret_cast<uint4*>(cur), n16,
+                                          static_cast<const unsigned char*>(src) + n16 * 16, static_cast<unsigned char*>(cur + n16 * 16),
+                                          int(a_bytes % 16)));
     }
     else
         CKB_CUDA_CHECK(cudaMemcpyAsync(cur, pp->a, a_bytes, cudaMemcpyHostToDevice, st));
