@@ -234,6 +234,7 @@ __global__ void __launch_bounds__(GG_THREADS, 2) grouped_gemm_kernel(const Group
             if(kt + 1 < KT) load_regs(kt + 1);
             const uint16_t* As = As_base + buf * GG_A_ELEMS;
             const uint16_t* Bs = Bs_base + buf * GG_B_ELEMS;
+            if(m0 + wm * 16 < Mg) // a warp whose 16 rows lie past M_g only converts and synchronises (48-row groups: a quarter of the MMAs)
 #pragma unroll
             for(int kq = 0; kq < GG_BK / 32; ++kq)
             {
@@ -281,6 +282,256 @@ __global__ void __launch_bounds__(GG_THREADS, 2) grouped_gemm_kernel(const Group
         {
             const int r = c >> 3, cc = (c & 7) * 8, m = m0 + r, n = n0 + cc;
             if(m >= Mg || n >= ga.N) continue; // N % 16 == 0 (host check): the 8 columns are all inside
+            const float* p0 = red + r * GG_RED_PITCH + cc;
+            const float* p1 = p0 + GG_BM * GG_RED_PITCH;
+            float v[8];
+#pragma unroll
+            for(int q = 0; q < 8; q += 4)
+            {
+                const float4 x = *reinterpret_cast<const float4*>(p0 + q), y = *reinterpret_cast<const float4*>(p1 + q);
+                v[q] = x.x + y.x; v[q + 1] = x.y + y.y; v[q + 2] = x.z + y.z; v[q + 3] = x.w + y.w;
+            }
+            uint32_t o[4];
+#pragma unroll
+            for(int q = 0; q < 8; q += 2)
+            {
+                float d0 = 0.f, d1 = 0.f;
+                if(D0)
+                {
+                    const long long off = m * ldd + n + q;
+                    if(ga.d_dtype == CKB_F32) { d0 = static_cast<const float*>(D0)[off]; d1 = static_cast<const float*>(D0)[off + 1]; }
+                    else { d0 = bf16_bits_to_f32(static_cast<const uint16_t*>(D0)[off]); d1 = bf16_bits_to_f32(static_cast<const uint16_t*>(D0)[off + 1]); }
+                }
+                const float e0 = cde_apply_f32(ep, v[q], d0, 0.f), e1 = cde_apply_f32(ep, v[q + 1], d1, 0.f);
+                o[q >> 1] = uint32_t(f32_to_bf16_bits(e0, ga.flags)) | (uint32_t(f32_to_bf16_bits(e1, ga.flags)) << 16);
+            }
+            uint16_t* dst = E + m * lde + n;
+            if((reinterpret_cast<uintptr_t>(dst) & 15) == 0) *reinterpret_cast<uint4*>(dst) = make_uint4(o[0], o[1], o[2], o[3]);
+            else
+            {
+#pragma unroll
+                for(int q = 0; q < 4; ++q) *reinterpret_cast<uint32_t*>(dst + 2 * q) = o[q];
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------------
+// Round-2 form for row-major A (mk_nk_mn / mk_kn_mn): the same tiles, fragments and arithmetic as the kernel above, but the tile's
+// loads are no longer one stage ahead of the math.  ncu on the kernel above (profiles/r1_grouped_ncu_summary.txt) shows a tile as
+// KT serial round trips to HBM (each stage's loads are issued when the previous stage starts its MMAs, and a client-31 tile has
+// only 4 stages); here G3_ST = 4 stages are in flight from the start of the tile: A through cp.async into a 4-slot ring (no
+// registers), the int8 weight through 4 rotating register sets (it is converted on its way into shared memory, so it has to pass
+// through registers anyway).  A client-31 tile (K = 512) therefore waits for HBM once.
+constexpr int G3_ST   = 4;
+constexpr int G3_SMEM = (G3_ST * GG_A_ELEMS + 2 * GG_B_ELEMS) * 2 + GG_BN * 4;
+static_assert(2 * G3_SMEM + 2048 <= 228 * 1024, "two CTAs per SM");
+
+__device__ __forceinline__ void cp_async_16(uint32_t dst, const void* src, int src_bytes)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+template <bool B_ROW, int CDE>
+__global__ void __launch_bounds__(GG_THREADS, 2) grouped_gemm_kernel_v3(const GroupedArgs ga)
+{
+    extern __shared__ __align__(16) unsigned char gg_smem[];
+    uint16_t* const As_base = reinterpret_cast<uint16_t*>(gg_smem);
+    uint16_t* const Bs_base = As_base + G3_ST * GG_A_ELEMS;
+    float* const s_scale    = reinterpret_cast<float*>(Bs_base + 2 * GG_B_ELEMS);
+    float* const red        = reinterpret_cast<float*>(gg_smem); // [2 k-halves][64][GG_RED_PITCH], aliases A slots 0 and 1
+    constexpr int BP        = B_ROW ? GG_PITCH_N : GG_PITCH_K;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, wm = warp & 3, wk = warp >> 2;
+    const int NT = (ga.N + GG_BN - 1) / GG_BN;
+    const int KT = (ga.K + GG_BK - 1) / GG_BK;
+    int buf = 0;
+
+    for(int t = blockIdx.x;; t += gridDim.x)
+    {
+        // ---- locate tile t (same walk as above) ------------------------------------------------------------
+        int g = ga.G, base = 0, Mg = 0;
+        for(int c = 0; c < ga.G; c += 32)
+        {
+            const int gi  = c + lane;
+            const int Ml  = gi < ga.G ? arg_field<int>(ga.args + size_t(gi) * ga.L.stride, ga.L.off_m) : 0;
+            const int cnt = ((Ml + GG_BM - 1) / GG_BM) * NT;
+            int incl      = cnt;
+#pragma unroll
+            for(int d = 1; d < 32; d <<= 1)
+            {
+                const int v = __shfl_up_sync(0xffffffffu, incl, d);
+                if(lane >= d) incl += v;
+            }
+            const unsigned hit = __ballot_sync(0xffffffffu, gi < ga.G && t < base + incl);
+            if(hit)
+            {
+                const int src = __ffs(hit) - 1;
+                g             = c + src;
+                Mg            = __shfl_sync(0xffffffffu, Ml, src);
+                base += __shfl_sync(0xffffffffu, incl - cnt, src);
+                break;
+            }
+            base += __shfl_sync(0xffffffffu, incl, 31);
+        }
+        if(g >= ga.G) break;
+        const unsigned char* ap = ga.args + size_t(g) * ga.L.stride;
+        const int m0 = ((t - base) / NT) * GG_BM, n0 = ((t - base) % NT) * GG_BN;
+        const uint16_t* A   = arg_field<const uint16_t*>(ap, ga.L.off_a);
+        const int8_t* B     = arg_field<const int8_t*>(ap, ga.L.off_b0);
+        const long long lda = arg_field<int>(ap, ga.L.off_sa), ldb = arg_field<int>(ap, ga.L.off_sb0);
+
+        // this thread's two 16-byte pieces of a weight stage: (row r, 16 codes from cc); the same (r, cc) in every stage
+        const int b_r0 = B_ROW ? tid >> 2 : tid >> 3, b_cc = B_ROW ? (tid & 3) * 16 : (tid & 7) * 16;
+        constexpr int B_DR = B_ROW ? GG_THREADS / 4 : GG_THREADS / 8; // row step between the two pieces
+        auto load_b = [&](int kt, uint4* rb) {
+            const int k0 = kt * GG_BK;
+#pragma unroll
+            for(int i = 0; i < 2; ++i)
+            {
+                const int r = b_r0 + i * B_DR;
+                const int k = B_ROW ? k0 + r : k0 + b_cc, n = B_ROW ? n0 + b_cc : n0 + r;
+                const bool ok = k < ga.K && n < ga.N;
+                rb[i] = ok ? *reinterpret_cast<const uint4*>(B_ROW ? B + k * ldb + n : B + n * ldb + k) : make_uint4(0, 0, 0, 0);
+            }
+        };
+        // A stage kt -> ring slot `slot`: rows past M_g repeat the last row (never stored), k past K is zero-filled
+        const int a_r0 = tid >> 4, a_kc = (tid & 15) * 8;
+        auto issue_a = [&](int kt, int slot) {
+            const int k0       = kt * GG_BK;
+            const bool ok      = k0 + a_kc < ga.K;
+            const uint32_t dst = ptx::smem_u32(As_base + slot * GG_A_ELEMS + a_r0 * GG_PITCH_K + a_kc);
+#pragma unroll
+            for(int i = 0; i < 4; ++i)
+            {
+                const int m = min(m0 + a_r0 + 16 * i, Mg - 1);
+                cp_async_16(dst + i * (16 * GG_PITCH_K * 2), ok ? static_cast<const void*>(A + m * lda + k0 + a_kc) : static_cast<const void*>(A), ok ? 16 : 0);
+            }
+        };
+        auto convert_b = [&](const uint4* rb, int b) {
+            uint16_t* Bs = Bs_base + b * GG_B_ELEMS;
+#pragma unroll
+            for(int i = 0; i < 2; ++i)
+            {
+                const int r = b_r0 + i * B_DR;
+                const uint32_t w[4] = {rb[i].x ^ 0x80808080u, rb[i].y ^ 0x80808080u, rb[i].z ^ 0x80808080u, rb[i].w ^ 0x80808080u};
+                uint32_t o[8];
+                if(B_ROW)
+                {
+#pragma unroll
+                    for(int j = 0; j < 8; j += 2)
+                    {
+                        const float4 s = *reinterpret_cast<const float4*>(s_scale + b_cc + 2 * j); // 16 codes along n: one scale each
+                        o[j]     = mul_pair_bf16<0>(w[j >> 1], s.x, s.y);
+                        o[j + 1] = mul_pair_bf16<2>(w[j >> 1], s.z, s.w);
+                    }
+                }
+                else
+                {
+                    const float s = s_scale[r]; // 16 codes along k of channel r
+#pragma unroll
+                    for(int j = 0; j < 8; j += 2)
+                    {
+                        o[j]     = mul_pair_bf16<0>(w[j >> 1], s, s);
+                        o[j + 1] = mul_pair_bf16<2>(w[j >> 1], s, s);
+                    }
+                }
+                *reinterpret_cast<uint4*>(Bs + r * BP + b_cc)     = make_uint4(o[0], o[1], o[2], o[3]);
+                *reinterpret_cast<uint4*>(Bs + r * BP + b_cc + 8) = make_uint4(o[4], o[5], o[6], o[7]);
+            }
+        };
+
+        uint4 rb[G3_ST][2];
+#pragma unroll
+        for(int j = 0; j < G3_ST; ++j)
+            if(j < KT) load_b(j, rb[j]);
+        if(tid < GG_BN)
+        {
+            float s = 1.f;
+            if(ga.has_scale && n0 + tid < ga.N) s = bf16_bits_to_f32(arg_field<const uint16_t*>(ap, ga.L.off_b1)[n0 + tid]);
+            s_scale[tid] = s;
+        }
+        float acc[8][4];
+#pragma unroll
+        for(int i = 0; i < 8; ++i) acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.f;
+
+        __syncthreads(); // s_scale visible; every warp is done with the previous tile's reduction area (A slots 0, 1)
+#pragma unroll
+        for(int j = 0; j < G3_ST; ++j)
+        {
+            if(j < KT) issue_a(j, j);
+            cp_async_commit();
+        }
+        // cp.async groups: stage s is group s (the prologue commits stages 0..3; iteration kt >= 1 commits stage kt + 3, possibly
+        // empty), so at iteration kt at most G3_ST - 2 younger groups may still be pending when stage kt is needed
+        for(int kt0 = 0; kt0 < KT; kt0 += G3_ST)
+        {
+#pragma unroll
+            for(int j = 0; j < G3_ST; ++j)
+            {
+                const int kt = kt0 + j; // ring slot of stage kt = j
+                if(kt < KT)
+                {
+                    convert_b(rb[j], buf);
+                    if(kt + G3_ST < KT) load_b(kt + G3_ST, rb[j]);
+                    cp_async_wait<G3_ST - 2>();
+                    __syncthreads(); // stage kt (A slot j, Bs[buf]) visible; every warp is done with the MMAs of stage kt - 1
+                    if(kt >= 1)
+                    {
+                        if(kt - 1 + G3_ST < KT) issue_a(kt - 1 + G3_ST, (j + G3_ST - 1) % G3_ST);
+                        cp_async_commit();
+                    }
+                    const uint16_t* As = As_base + j * GG_A_ELEMS;
+                    const uint16_t* Bs = Bs_base + buf * GG_B_ELEMS;
+                    if(m0 + wm * 16 < Mg)
+#pragma unroll
+                    for(int kq = 0; kq < GG_BK / 32; ++kq)
+                    {
+                        const int ks = wk * (GG_BK / 32) + kq;
+                        uint32_t af[4];
+                        ldmatrix_x4(ptx::smem_u32(As + (wm * 16 + (lane & 15)) * GG_PITCH_K + ks * 16 + (lane >> 4) * 8), af);
+#pragma unroll
+                        for(int np = 0; np < 4; ++np)
+                        {
+                            uint32_t bf[4];
+                            if(B_ROW)
+                                ldmatrix_x4_trans(ptx::smem_u32(Bs + (ks * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * BP + np * 16 + (lane >> 4) * 8), bf);
+                            else
+                                ldmatrix_x4(ptx::smem_u32(Bs + (np * 16 + (lane & 7) + (lane >> 4) * 8) * BP + ks * 16 + ((lane >> 3) & 1) * 8), bf);
+                            ptx::mma_m16n8k16<false>(acc[2 * np], af, bf[0], bf[1]);
+                            ptx::mma_m16n8k16<false>(acc[2 * np + 1], af, bf[2], bf[3]);
+                        }
+                    }
+                    buf ^= 1;
+                }
+            }
+        }
+        cp_async_wait<0>();
+        __syncthreads(); // all MMAs of the last stage are done: A slots 0 and 1 may be overwritten
+        {
+            float* my = red + wk * (GG_BM * GG_RED_PITCH) + (wm * 16 + (lane >> 2)) * GG_RED_PITCH + (lane & 3) * 2;
+#pragma unroll
+            for(int nt = 0; nt < 8; ++nt)
+            {
+                *reinterpret_cast<float2*>(my + nt * 8)                    = make_float2(acc[nt][0], acc[nt][1]);
+                *reinterpret_cast<float2*>(my + 8 * GG_RED_PITCH + nt * 8) = make_float2(acc[nt][2], acc[nt][3]);
+            }
+        }
+        __syncthreads();
+        EpiParams ep{};
+        ep.cde_op = CDE; ep.flags = ga.flags; ep.e_dtype = CKB_BF16; ep.d_dtype[0] = CKB_BF16;
+        uint16_t* E         = arg_field<uint16_t*>(ap, ga.L.off_e);
+        const long long lde = arg_field<int>(ap, ga.L.off_se);
+        const void* D0      = ga.num_d ? arg_field<const void*>(ap, ga.L.off_d0) : nullptr;
+        const long long ldd = ga.num_d ? arg_field<int>(ap, ga.L.off_sd0) : 0;
+#pragma unroll 1
+        for(int c = tid; c < GG_BM * GG_BN / 8; c += GG_THREADS)
+        {
+            const int r = c >> 3, cc = (c & 7) * 8, m = m0 + r, n = n0 + cc;
+            if(m >= Mg || n >= ga.N) continue;
             const float* p0 = red + r * GG_RED_PITCH + cc;
             const float* p1 = p0 + GG_BM * GG_RED_PITCH;
             float v[8];
@@ -419,16 +670,28 @@ int run_grouped(const ckb_gemm_problem& p, const void* dev_args, int group_count
     const long long NT    = (p.N + GG_BN - 1) / GG_BN;
     const long long tiles = ((long long)(sum_m + GG_BM - 1) / GG_BM + group_count) * NT; // upper bound on the tile count
     const int grid        = int(std::min<long long>(tiles, 3LL * device_info().sm_count));
-    auto go = [&](auto kern) -> int {
-        CKB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GG_SMEM)); // cheap, idempotent
-        kern<<<grid, GG_THREADS, GG_SMEM, stream>>>(ga);
+    // row-major A: the form with four stages in flight (cp.async ring); column-major A (transposed on its way into shared memory)
+    // and short K use the register-prefetch form
+    // (CKB_GROUPED_KERNEL=1 / 3 forces one of them for A/B measurements)
+    const char* force = getenv("CKB_GROUPED_KERNEL");
+    // measured (profiles/r2_grouped_ab.txt): the deeper pipeline pays from K ~ 2048 up (5 - 14 %); below that its longer prologue costs
+    // more than the overlap returns (K = 512: 16.4 vs 14.4 us), the per-stage cost being conversion + MMA issue, not HBM latency
+    const bool v3     = !ga.a_col && ((force && *force) ? atoi(force) == 3 : p.K >= 2048);
+    auto go = [&](auto kern, int smem) -> int {
+        CKB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); // cheap, idempotent
+        CKB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        kern<<<grid, GG_THREADS, smem, stream>>>(ga);
         return CKB_OK;
     };
     const bool row = p.b_layout == CKB_ROW;
     int rc = CKB_OK;
     switch(p.cde_op)
     {
-#define GG_CASE(op) case op: rc = row ? go(grouped_gemm_kernel<true, op>) : go(grouped_gemm_kernel<false, op>); break;
+#define GG_CASE(op)                                                                                                              \
+    case op:                                                                                                                     \
+        if(v3) rc = row ? go(grouped_gemm_kernel_v3<true, op>, G3_SMEM) : go(grouped_gemm_kernel_v3<false, op>, G3_SMEM);        \
+        else rc = row ? go(grouped_gemm_kernel<true, op>, GG_SMEM) : go(grouped_gemm_kernel<false, op>, GG_SMEM);                \
+        break;
         GG_CASE(CKB_CDE_PASSTHROUGH) GG_CASE(CKB_CDE_ADD) GG_CASE(CKB_CDE_FASTGELU) GG_CASE(CKB_CDE_ADD_FASTGELU)
         GG_CASE(CKB_CDE_MULTIPLY) GG_CASE(CKB_CDE_MULTIPLY_FASTGELU)
 #undef GG_CASE
