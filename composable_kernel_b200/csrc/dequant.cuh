@@ -152,12 +152,26 @@ __device__ __forceinline__ float s8_byte_to_f32(uint32_t w_biased, int byte)
     return __uint_as_float(prmt(w_biased, 0x4B000000u, sel)) - 8388736.0f;
 }
 
+// q * s in ONE FFMA per code, exactly: the biased byte b = q + 128 is placed in mantissa bits 8..15 of 2^15 (0x4700bb00 = 2^15 + b,
+// one PRMT), and fma(2^15 + b, s, -(2^15 + 128) s) = (b - 128) s = q s.  Exact because the FFMA rounds the exact sum once and q s has
+// <= 16 significant bits (s is a bf16 value); the addend -(2^15 + 128) s = -2^7 * 257 * s has <= 17 bits, so it is exact as well.
+// (3 instead of 4 instructions per code with the final pack; these kernels are issue-bound on the conversion.)  The only
+// difference from (float(q)) * s is the SIGN of a zero weight under a negative scale (+0 instead of -0), which cannot reach a GEMM
+// output: the accumulators start at +0 and (+0) + (-0) = +0.  Domain: |s| < 2^112 (beyond it the addend overflows; checked exhaustively
+// over all finite bf16 scales x all 256 codes, tests/test_host_logic.py::test_int8_scale_fma_identity).
+__device__ __forceinline__ float s8_biased_byte_times_scale(uint32_t w_biased, int byte, float scale, float neg_bias_scale)
+{
+    const uint32_t sel = 0x7404u | (uint32_t(byte) << 4); // [0x47, 0x00, byte, 0x00] of (w, 0x47000000)
+    return fmaf(__uint_as_float(prmt(w_biased, 0x47000000u, sel)), scale, neg_bias_scale);
+}
+
 // Multiply<bhalf_t,int8_t,bhalf_t>: truncate(float(q) * float(s)) -- q*s is exact in fp32 (8 x 8 bits)
 __device__ __forceinline__ void dequant_s8x4_mul_bf16(uint32_t w, float scale, uint32_t* out2)
 {
     const uint32_t wb = w ^ 0x80808080u;
-    const float f0 = s8_byte_to_f32(wb, 0) * scale, f1 = s8_byte_to_f32(wb, 1) * scale;
-    const float f2 = s8_byte_to_f32(wb, 2) * scale, f3 = s8_byte_to_f32(wb, 3) * scale;
+    const float nb = scale * -32896.0f;
+    const float f0 = s8_biased_byte_times_scale(wb, 0, scale, nb), f1 = s8_biased_byte_times_scale(wb, 1, scale, nb);
+    const float f2 = s8_biased_byte_times_scale(wb, 2, scale, nb), f3 = s8_biased_byte_times_scale(wb, 3, scale, nb);
     out2[0] = prmt(__float_as_uint(f0), __float_as_uint(f1), 0x7632); // high halves: truncation
     out2[1] = prmt(__float_as_uint(f2), __float_as_uint(f3), 0x7632);
 }

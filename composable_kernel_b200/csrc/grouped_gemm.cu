@@ -67,11 +67,13 @@ __device__ __forceinline__ void ldmatrix_x4_trans(uint32_t addr, uint32_t* r)
 // two int8 codes (bytes i, i+1 of wx = w ^ 0x80808080, i.e. q + 128) times their scales -> packed truncated bf16 pair.
 // 0x4B000000 | (q + 128) is the float 2^23 + q + 128, so one PRMT and one exact FADD give float(q) without the
 // quarter-rate I2F; the product with the bf16 scale is exact in fp32 (8-bit x 8-bit significands).
+// Round 2: one PRMT + one FFMA per code (dequant.cuh, s8_biased_byte_times_scale: fma(2^15 + q + 128, s, -(2^15 + 128) s) = q s
+// exactly); n0 / n1 = -32896 * s0 / s1.
 template <int I>
-__device__ __forceinline__ uint32_t mul_pair_bf16(uint32_t wx, float s0, float s1)
+__device__ __forceinline__ uint32_t mul_pair_bf16(uint32_t wx, float s0, float s1, float n0, float n1)
 {
-    const float f0 = (__uint_as_float(__byte_perm(wx, 0x4B000000u, 0x7540 | I)) - 8388736.f) * s0;
-    const float f1 = (__uint_as_float(__byte_perm(wx, 0x4B000000u, 0x7540 | (I + 1))) - 8388736.f) * s1;
+    const float f0 = fmaf(__uint_as_float(__byte_perm(wx, 0x47000000u, 0x7404 | (I << 4))), s0, n0);
+    const float f1 = fmaf(__uint_as_float(__byte_perm(wx, 0x47000000u, 0x7404 | ((I + 1) << 4))), s1, n1);
     return __byte_perm(__float_as_uint(f0), __float_as_uint(f1), 0x7632); // {hi16(f1), hi16(f0)}: truncation
 }
 
@@ -214,8 +216,8 @@ __global__ void __launch_bounds__(GG_THREADS, 2) grouped_gemm_kernel(const Group
                     // 16 consecutive codes: along n at fixed k (B_ROW: one scale each) or along k at fixed n
                     const float s0 = B_ROW ? s_scale[cc + 2 * j] : s_scale[r], s1 = B_ROW ? s_scale[cc + 2 * j + 1] : s0;
                     const float s2 = B_ROW ? s_scale[cc + 2 * j + 2] : s0, s3 = B_ROW ? s_scale[cc + 2 * j + 3] : s0;
-                    o[j]     = mul_pair_bf16<0>(w[j >> 1], s0, s1);
-                    o[j + 1] = mul_pair_bf16<2>(w[j >> 1], s2, s3);
+                    o[j]     = mul_pair_bf16<0>(w[j >> 1], s0, s1, s0 * -32896.f, s1 * -32896.f);
+                    o[j + 1] = mul_pair_bf16<2>(w[j >> 1], s2, s3, s2 * -32896.f, s3 * -32896.f);
                 }
                 *reinterpret_cast<uint4*>(Bs + r * BP + cc)     = make_uint4(o[0], o[1], o[2], o[3]);
                 *reinterpret_cast<uint4*>(Bs + r * BP + cc + 8) = make_uint4(o[4], o[5], o[6], o[7]);
@@ -425,18 +427,18 @@ __global__ void __launch_bounds__(GG_THREADS, 2) grouped_gemm_kernel_v3(const Gr
                     for(int j = 0; j < 8; j += 2)
                     {
                         const float4 s = *reinterpret_cast<const float4*>(s_scale + b_cc + 2 * j); // 16 codes along n: one scale each
-                        o[j]     = mul_pair_bf16<0>(w[j >> 1], s.x, s.y);
-                        o[j + 1] = mul_pair_bf16<2>(w[j >> 1], s.z, s.w);
+                        o[j]     = mul_pair_bf16<0>(w[j >> 1], s.x, s.y, s.x * -32896.f, s.y * -32896.f);
+                        o[j + 1] = mul_pair_bf16<2>(w[j >> 1], s.z, s.w, s.z * -32896.f, s.w * -32896.f);
                     }
                 }
                 else
                 {
-                    const float s = s_scale[r]; // 16 codes along k of channel r
+                    const float s = s_scale[r], ns = s * -32896.f; // 16 codes along k of channel r
 #pragma unroll
                     for(int j = 0; j < 8; j += 2)
                     {
-                        o[j]     = mul_pair_bf16<0>(w[j >> 1], s, s);
-                        o[j + 1] = mul_pair_bf16<2>(w[j >> 1], s, s);
+                        o[j]     = mul_pair_bf16<0>(w[j >> 1], s, s, ns, ns);
+                        o[j + 1] = mul_pair_bf16<2>(w[j >> 1], s, s, ns, ns);
                     }
                 }
                 *reinterpret_cast<uint4*>(Bs + r * BP + b_cc)     = make_uint4(o[0], o[1], o[2], o[3]);

@@ -205,3 +205,24 @@ def test_oracle_and_host_layer_under_asan_ubsan():
         pytest.skip("no sanitizer runtime for the host compiler here: " + r.stderr[-200:])
     r = subprocess.run([os.path.join(root, "oracle", "_san", "sanitize_main")], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "sanitize_main: OK" in r.stdout, (r.stdout[-1500:], r.stderr[-3000:])
+
+
+def test_int8_scale_fma_identity():
+    """The device conversion of the int8 `Multiply` weight (csrc/dequant.cuh, s8_biased_byte_times_scale): one FFMA per code,
+    fma(2^15 + q + 128, s, -(2^15 + 128) s), must equal float(q) * float(s) bit for bit (binary_element_wise_operation.hpp:184-190
+    multiplies in fp32) for every code and every finite bf16 scale below 2^112; zeros may differ in sign only."""
+    bits = np.arange(65536, dtype=np.uint32)
+    s = (bits << 16).view(np.float32)
+    s = s[np.isfinite(s) & (np.abs(s) < 2.0 ** 112)]
+    q = np.arange(-128, 128, dtype=np.int32)
+    xf = (np.uint32(0x47000000) | ((q + 128).astype(np.uint32) << 8)).view(np.float32)
+    assert np.array_equal(xf, (32768 + q + 128).astype(np.float32))
+    with np.errstate(all="ignore"):
+        nb = (s * np.float32(-32896.0)).astype(np.float32)
+        assert np.array_equal(nb.astype(np.float64), s.astype(np.float64) * -32896.0)  # the addend is exact
+        ref = q.astype(np.float32)[None, :] * s[:, None]
+        # float64 holds the product (24 + 8 bits) and the sum exactly: one rounding to fp32 = the FFMA
+        new = (xf.astype(np.float64)[None, :] * s.astype(np.float64)[:, None] + nb.astype(np.float64)[:, None]).astype(np.float32)
+    same = ref.view(np.uint32) == new.view(np.uint32)
+    both_zero = (ref == 0) & (new == 0)
+    assert np.all(same | both_zero)
