@@ -96,6 +96,10 @@ def lib():
             l.ckb_gemv_schedule.argtypes = [C.c_int32] * 6 + [C.POINTER(C.c_int32)]
             l.ckb_transpose_a_colmajor.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
             l.ckb_peer_wait.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+        if hasattr(l, "ckb_gemm_run_static_scratch"):   # absent from older experiment builds selected with CKB_LIB
+            l.ckb_static_scratch_bytes.argtypes = []
+            l.ckb_static_scratch_bytes.restype = C.c_uint64
+            l.ckb_gemm_run_static_scratch.argtypes = [C.POINTER(GemmProblem), C.POINTER(GemmPlan), C.c_void_p]
         l.ckb_grouped_gemm_arg_bytes.argtypes = [C.c_int32, C.c_int32]
         l.ckb_grouped_gemm_arg_bytes.restype = C.c_uint64
         l.ckb_grouped_gemm_query.argtypes = [C.POINTER(GemmProblem), C.c_int32]
@@ -109,6 +113,7 @@ EXPORTED = [
     "ckb_prepack_b_u8", "ckb_prepack_b_rowmajor_i8", "ckb_prepack_b_int4_bytes", "ckb_prepack_b_int4", "ckb_grouped_gemm_run", "ckb_grouped_gemm_query", "ckb_grouped_gemm_arg_bytes",
     "ckb_last_error", "ckb_version", "ckb_device_sm_count", "ckb_peer_wait",
     "ckb_tile_coord", "ckb_streamk_range", "ckb_gemv_schedule", "ckb_transpose_a_colmajor",
+    "ckb_static_scratch_bytes", "ckb_gemm_run_static_scratch",
 ]
 
 

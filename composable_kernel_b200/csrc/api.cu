@@ -345,6 +345,20 @@ int ckb_gemm_run(const ckb_gemm_problem* pp, const ckb_gemm_plan* plan, void* wo
     }
 }
 
+uint64_t ckb_static_scratch_bytes(void) { return CKB_STATIC_SCRATCH_BYTES; }
+
+int ckb_gemm_run_static_scratch(const ckb_gemm_problem* pp, const ckb_gemm_plan* plan, void* stream)
+{
+    if(!pp || !plan) return set_error(CKB_ERR_INVALID, "null problem/plan");
+    if(!plan->supported) return set_error(CKB_ERR_UNSUPPORTED, "plan is not supported: %s", last_error().c_str());
+    if(plan->kernel_id != KID_WQ_DECODE)
+        return set_error(CKB_ERR_UNSUPPORTED, "static scratch: kernel %s uses no scratch memory; call ckb_gemm_run with workspace = NULL", plan->kernel_name);
+    if(pp->M > 64) return set_error(CKB_ERR_UNSUPPORTED, "static scratch: M = %d; this entry point serves one launch of the decode kernel (M <= 64)", pp->M);
+    if(pp->M == 0 || pp->N == 0) return CKB_OK;
+    if(!device_info().ok) return set_error(CKB_ERR_NO_DEVICE, "no sm_100 device");
+    return run_wq_decode_static(*pp, *plan, static_cast<cudaStream_t>(stream));
+}
+
 uint64_t ckb_gemm_host_staging_bytes(const ckb_gemm_problem* p)
 {
     if(!p) return 0;

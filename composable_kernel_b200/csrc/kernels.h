@@ -44,6 +44,8 @@ int plan_wq_fused(const ckb_gemm_problem& p, ckb_gemm_plan& plan);
 int run_wq_fused(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStream_t stream);
 int plan_wq_decode(const ckb_gemm_problem& p, ckb_gemm_plan& plan);
 int run_wq_decode(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, void* workspace, cudaStream_t stream);
+// the same launch with the scratch in the library's own static device array (ckb_gemm_run_static_scratch, ckb.h): no allocation
+int run_wq_decode_static(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStream_t stream);
 int plan_wq_gemv(const ckb_gemm_problem& p, ckb_gemm_plan& plan);
 int run_wq_gemv(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStream_t stream);
 // schedule of the W4 decode kernel (host arithmetic only: exercised on CPU through ckb_gemv_schedule)

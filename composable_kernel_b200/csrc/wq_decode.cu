@@ -757,4 +757,35 @@ int run_wq_decode(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, void* wo
     return dispatch_decode_n(wp->n_mma, wf, f16, wp, a, plan, stream);
 }
 
+// ---- ckb_gemm_run_static_scratch (ckb.h): the stream-K scratch in a static device array, for callers that may not allocate ----
+// One array per device that loads the library (held until exit), shared by every call on that device.  The NAME below is a
+// host-side stand-in in host code, not a device address: the address the kernel gets comes from cudaGetSymbolAddress, asked once
+// per device with that device current.
+static __device__ __align__(256) unsigned char g_static_scratch[CKB_STATIC_SCRATCH_BYTES];
+
+int run_wq_decode_static(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStream_t stream)
+{
+    if(plan.workspace_bytes > uint64_t(CKB_STATIC_SCRATCH_BYTES))
+        return set_error(CKB_ERR_WORKSPACE, "static scratch: this problem needs %llu bytes of scratch, the built-in array holds %u (use ckb_gemm_run with a caller workspace)",
+                         (unsigned long long)plan.workspace_bytes, unsigned(CKB_STATIC_SCRATCH_BYTES));
+    if(getenv("CKB_GTRACE") || getenv("CKB_TRACE"))
+        return set_error(CKB_ERR_INVALID, "static scratch: the CKB_GTRACE / CKB_TRACE debug recorders allocate device memory; unset them for this entry point");
+    constexpr int MAX_DEV = 64;
+    static void* dev_ptr[MAX_DEV]; // per device ordinal; written once (the address never changes), read with acquire
+    int dev = 0;
+    CKB_CUDA_CHECK(cudaGetDevice(&dev));
+    if(dev < 0 || dev >= MAX_DEV) return set_error(CKB_ERR_INVALID, "static scratch: device ordinal %d is out of range", dev);
+    void* ptr = __atomic_load_n(&dev_ptr[dev], __ATOMIC_ACQUIRE);
+    if(!ptr)
+    {
+        CKB_CUDA_CHECK(cudaGetSymbolAddress(&ptr, g_static_scratch)); // the current device's copy of the array
+        if(!ptr) return set_error(CKB_ERR_INVALID, "static scratch: cudaGetSymbolAddress returned a null address");
+        __atomic_store_n(&dev_ptr[dev], ptr, __ATOMIC_RELEASE);
+    }
+    // partial tiles and arrival counters must start at zero; the array keeps whatever the last call (possibly a failed or
+    // differently shaped one) left behind, so the part this launch uses is cleared every time, in stream order
+    CKB_CUDA_CHECK(cudaMemsetAsync(ptr, 0, size_t(plan.workspace_bytes), stream));
+    return run_wq_decode(p, plan, ptr, stream);
+}
+
 } // namespace ckb

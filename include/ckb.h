@@ -196,6 +196,22 @@ int ckb_gemm_query(const ckb_gemm_problem* problem, ckb_gemm_plan* plan);
 /* Launch on `stream`.  `plan` must come from ckb_gemm_query on the same problem (same pointers). */
 int ckb_gemm_run(const ckb_gemm_problem* problem, const ckb_gemm_plan* plan, void* workspace, void* stream);
 
+/* Allocation-free variant of ckb_gemm_run for the one kernel family that needs scratch memory at decode sizes (the stream-K
+   tcgen05 decode kernel, plan->kernel_name "wq_decode_*": int8-weight formats behind CKB_FLAG_W8_STREAMK, M <= 64 rows).
+   NO counterpart in the reference: added for callers that cannot call
+   cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).  The scratch (fp32 partial
+   tiles + per-tile arrival counters, plan->workspace_bytes) lives in a file-scope `static __device__` array of
+   CKB_STATIC_SCRATCH_BYTES inside the library, which every GPU that loads the library holds until the process exits.  The call
+   allocates nothing (no cudaMalloc / cudaFree / allocating library routine): it clears the part of the array it uses
+   (cudaMemsetAsync on `stream`) and launches the same kernel as ckb_gemm_run, so results equal ckb_gemm_run's.
+   Limits: plan->workspace_bytes <= CKB_STATIC_SCRATCH_BYTES (8 MiB: N <= 28672 at M <= 64), else CKB_ERR_WORKSPACE; plans of
+   other kernels (which need no scratch: use ckb_gemm_run with workspace = NULL) and M > 64 are CKB_ERR_UNSUPPORTED.
+   EVERY call on a device shares the one array: calls that may overlap on the GPU (different streams, concurrent graph branches)
+   race on it -- keep them on one stream or order them yourself. */
+#define CKB_STATIC_SCRATCH_BYTES (8u << 20)
+uint64_t ckb_static_scratch_bytes(void);
+int ckb_gemm_run_static_scratch(const ckb_gemm_problem* problem, const ckb_gemm_plan* plan, void* stream);
+
 /* Host-buffer convenience used for end-to-end measurement: A, D and E are HOST pointers (pinned or
    pageable); weights/scales stay device-resident.  Copies A (and D) host->device, runs, copies E
    device->host, synchronises the stream.  `staging` = device scratch of ckb_gemm_host_staging_bytes(). */
