@@ -31,7 +31,29 @@ int launch_gemv2_variant(bool f16, int nt, int gw, int kbu, const G2Plan* gp, co
 
 // Host-side schedule of the decode kernel (also exercised without a GPU by tests/test_capi_cpu.py through
 // ckb_gemv_schedule): how the n16 channel groups and the K range are cut into (CTA, pass, stage, warp) work.
+static int schedule_wq_gemv2_cap(int M, int N, int K, bool zp, int sms, G2Sched& s, int mode, int gcap);
+
 int schedule_wq_gemv2(int M, int N, int K, bool zp, int sms, G2Sched& s, int mode)
+{
+    // groups per slot are capped by what a warp can hold; when even one ring stage of such a slot does not fit in shared memory
+    // (int8 weights: 1 KB per group and 64-k block, e.g. cfg3's N = 14336 -> 7 groups per CTA), the slots are made smaller: more
+    // passes.  A schedule with empty slots (more slots than groups) is not accepted: the kernel assumes every slot holds a group.
+    int gcap = 99;
+    for(;;)
+    {
+        const int rc = schedule_wq_gemv2_cap(M, N, K, zp, sms, s, mode, gcap);
+        if(rc == CKB_OK) return (gcap == 99 || s.slot_q >= 1) ? CKB_OK : set_error(CKB_ERR_UNSUPPORTED, "W8 decode kernel: no schedule without empty slots fits in shared memory");
+        if(!(mode & 8) || (mode & 1) || s.grid < 1 || s.passes < 1 || s.g_hi < 2) return rc;
+        // measured (profiles/r2_w8_multipass.txt): the multi-pass form beats the stream-K kernel by 10 - 20 % at 14336 x 4096 and loses
+        // 2 - 8 % at 28672 x 8192, where stream-K's ~10 us fixed cost no longer matters: refuse above 128 MiB of weights
+        if((unsigned long long)N * K >= (128ull << 20)) return rc;
+        const int per_cta = (s.n_groups + s.grid - 1) / s.grid;
+        gcap = std::min((per_cta + s.passes) / (s.passes + 1), s.g_hi - 1); // groups per slot with one more pass
+        if(gcap < 1) return rc;
+    }
+}
+
+static int schedule_wq_gemv2_cap(int M, int N, int K, bool zp, int sms, G2Sched& s, int mode, int gcap)
 {
     const bool w8 = mode & 8; // int8-weight formats: 1024 B per (16-channel group, 64-k block), no scale / zero-point rows in the stage
     const bool fixed = mode & 1, rtn = (mode & 2) || (mode & 4) || w8; // bit 2 (peer-store epilogue): 128-k units like RTN, fp32-scale numerics
@@ -45,7 +67,7 @@ int schedule_wq_gemv2(int M, int N, int K, bool zp, int sms, G2Sched& s, int mod
     s.grid     = std::max(1, std::min(sms, s.n_groups));
     s.grid     = std::max(1, std::min(env_int("CKB_GEMV_GRID", s.grid), s.n_groups));
     // groups per slot: up to 2 x GW with the warps split into two channel halves (M <= 8), GW otherwise
-    const int gmax    = std::max(1, std::min((s.nt == 1 ? 2 : 1) * gwmx, fixed ? 99 : env_int("CKB_G2_GMAX", 99)));
+    const int gmax    = std::max(1, std::min({(s.nt == 1 ? 2 : 1) * gwmx, fixed ? 99 : env_int("CKB_G2_GMAX", 99), gcap}));
     const int per_cta = (s.n_groups + s.grid - 1) / s.grid;
     s.passes  = (per_cta + gmax - 1) / gmax;
     s.n_slots = s.grid * s.passes;

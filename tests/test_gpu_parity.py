@@ -469,7 +469,8 @@ def test_torch_custom_ops_match_the_oracle():
     assert np.array_equal(H.from_dev_bf16(e), refe)
 
 
-@pytest.mark.parametrize("M,N,K,cde", [(8, 256, 512, "add"), (16, 4096, 4096, "pass"), (33, 384, 640, "add_gelu"), (1, 11008, 4096, "add")])
+@pytest.mark.parametrize("M,N,K,cde", [(8, 256, 512, "add"), (16, 4096, 4096, "pass"), (33, 384, 640, "add_gelu"), (1, 11008, 4096, "add"),
+                                       (16, 14336, 4096, "add"), (8, 14336, 1024, "add_gelu"), (3, 14336, 512, "pass")])  # cfg3's N: multi-pass slots
 def test_w8a16_decode_both_kernels_vs_oracle(M, N, K, cde):
     """int8-weight decode rows on the N-split HMMA kernel (default) and on the stream-K tcgen05 kernel (CKB_FLAG_W8_STREAMK,
     the second factory instance): same oracle, same tolerance"""

@@ -83,6 +83,25 @@ def test_decode_schedule_covers_the_problem_and_fits_the_sm(M, N, K, mode):
         assert s["kbu"] == 2
 
 
+@pytest.mark.parametrize("M", [1, 8, 16, 32])
+@pytest.mark.parametrize("N,K", [(4096, 4096), (11008, 4096), (14336, 4096), (28672, 8192), (4096, 14336), (1024, 512)])
+def test_decode_schedule_int8_weights_shrinks_slots_until_a_stage_fits(M, N, K):
+    """mode 8 (int8 weights, 1 KB per group and 64-k block): cfg3's N = 14336 gives 7 groups per CTA, whose ring stage does not fit
+    in shared memory -- the schedule then takes more passes with smaller slots instead of handing the shape to the stream-K kernel.
+    A schedule is either refused (the dispatcher falls back to stream-K) or has no empty slot."""
+    rc, s = sched(M, N, K, mode=8)
+    if rc != 0:
+        # 32-row activation stages leave room for one group per slot only (more slots than groups); above 128 MiB of weights the
+        # stream-K kernel is the faster one (profiles/r2_w8_multipass.txt)
+        assert M == 32 or N * K >= 128 << 20
+        return
+    assert s["slot_q"] >= 1 and s["slot_q"] * s["n_slots"] + s["slot_r"] == s["n_groups"] and s["n_slots"] == s["grid"] * s["passes"]
+    wn = 1 << s["wn_log2"]
+    assert s["gw"] * wn >= s["g_hi"] and s["kbu"] == 2
+    assert s["ring"] >= (2 if s["passes"] * s["n_chunks"] > 1 else 1)
+    assert s["ring"] * s["stage_bytes"] <= s["bar_off"] and s["smem_bytes"] <= 227 * 1024
+
+
 def test_fixed_k_order_schedule_is_shard_invariant():
     for M in (1, 16):
         ref = None
