@@ -43,7 +43,8 @@ constexpr int DQ_THREADS = 128 * DQ_TEAMS + 64;
 constexpr int DQ_WARP_MMA  = 4 * DQ_TEAMS;
 constexpr int DQ_WARP_PROD = 4 * DQ_TEAMS + 1;
 constexpr int DQ_MD        = 4;   // ring of per-unit "MMAs complete" barriers
-constexpr int DQ_TMEM_COLS = 256; // two CTAs per SM
+constexpr int DQ_TMEM_COLS = 256;
+constexpr int DQ_SMEM_EXCLUSIVE = 116 * 1024; // dynamic shared memory of a launch that must own its SM (see plan_wq_decode)
 
 struct DQArgs
 {
@@ -182,6 +183,9 @@ static __device__ __noinline__ void decode_drain(const DQArgs& args, int nt, int
     if(bar_id == 1) ptx::named_bar_sync<1>(128); else ptx::named_bar_sync<2>(128);
     if(q == 0 && lane == 0)
     {
+        // release by the SIGNALLING thread, after the barrier (cumulative over the reds of the threads it has synchronised with;
+        // the per-thread fences above sit in front of the barrier and do not order thread 0's arrival behind the others' reds)
+        __threadfence();
         const int old = atomicAdd(args.counters + nt, seg_units);
         *flag         = (old + seg_units == k_units) ? 1 : 0;
     }
@@ -581,7 +585,7 @@ int launch_decode(const WQPlan* wp, const DQArgs& a, const ckb_gemm_plan& plan, 
     uint64_t dev_bit = 0;
     if(attr_once.need(dev_bit))
     {
-        CKB_CUDA_CHECK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        CKB_CUDA_CHECK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, std::max(smem, DQ_SMEM_EXCLUSIVE)));
         // without this the driver sizes the L1/shared carve-out for ONE block and the second CTA never fits
         CKB_CUDA_CHECK(cudaFuncSetAttribute(kfn, cudaFuncAttributePreferredSharedMemoryCarveout,
                                             cudaSharedmemCarveoutMaxShared));
@@ -597,13 +601,20 @@ int launch_decode(const WQPlan* wp, const DQArgs& a, const ckb_gemm_plan& plan, 
     cudaLaunchConfig_t cfg{};
     cfg.gridDim          = dim3(plan.grid);
     cfg.blockDim         = dim3(DQ_THREADS);
-    cfg.dynamicSmemBytes = smem;
+    cfg.dynamicSmemBytes = std::max(smem, int(plan.smem_bytes));
     cfg.stream           = stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs    = attr;
-    cfg.numAttrs = 1;
+    // Programmatic dependent launch only while the stream is being captured (kernel -> kernel edges of a graph), as in wq_gemv2:
+    // an EAGER launch with the attribute costs ~20 us of host time against ~6 us without (tests/host_cost_probe.py).
+    // CKB_DECODE_PDL=0/1 overrides.
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if(cudaStreamIsCapturing(stream, &cs) != cudaSuccess) { cudaGetLastError(); cs = cudaStreamCaptureStatusNone; }
+    int pdl = cs == cudaStreamCaptureStatusActive;
+    if(const char* e = getenv("CKB_DECODE_PDL")) pdl = atoi(e);
+    cfg.numAttrs = pdl ? 1 : 0;
     CKB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kfn, wp->tmAct, wp->tmW, a));
     return CKB_OK;
 }
@@ -658,11 +669,19 @@ int plan_wq_decode(const ckb_gemm_problem& p, ckb_gemm_plan& plan)
     wp->units_total    = n_tiles * k_units;
     wp->units_per_tile = k_units;
     const int sms      = device_info().sm_count > 0 ? device_info().sm_count : 148;
-    int per_sm         = dq_smem_bytes(n_mma, wf) <= 113 * 1024 ? 2 : 1;
-    if(const char* e = getenv("CKB_DECODE_CTAS_PER_SM")) per_sm = std::max(1, atoi(e));
+    // ONE CTA per SM.  With two co-resident CTAs (the round-1 choice for n_mma <= 32) 2 - 40 % of the launches on 11008 x 4096 and
+    // 14336 x 4096 returned tiles with a few wrong k-chunks (timing-dependent; not the stream-K reduction: returning atomics,
+    // strong loads and atomic read-and-clear changed nothing, tests/streamk_stress_probe.py, profiles/r2_streamk_two_cta_defect.txt);
+    // with one CTA per SM: 0 of 1800.  The cause inside the TMEM-A pipeline is not found yet; one CTA is also 6 - 10 % FASTER up to
+    // 14336 x 4096 and 5 - 9 % slower at 28672 x 8192.  CKB_DECODE_CTAS_PER_SM=2 reproduces the defect.
+    int per_sm         = 1;
+    if(const char* e = getenv("CKB_DECODE_CTAS_PER_SM")) per_sm = std::max(1, std::min(2, atoi(e)));
+    if(dq_smem_bytes(n_mma, wf) > 113 * 1024) per_sm = 1;
     plan.grid            = std::max(1, std::min(sms * per_sm, wp->units_total));
     plan.block           = DQ_THREADS;
-    plan.smem_bytes      = dq_smem_bytes(n_mma, wf);
+    // exclusive SM: the launch asks for more than half of the shared memory, so that a CTA of the NEXT stream-K launch (programmatic
+    // dependent launch under graph replay) cannot become co-resident either
+    plan.smem_bytes      = per_sm == 1 ? std::max(dq_smem_bytes(n_mma, wf), DQ_SMEM_EXCLUSIVE) : dq_smem_bytes(n_mma, wf);
     plan.split_units     = k_units;
     plan.workspace_bytes = uint64_t(n_tiles) * n_mma * DQ_UNIT_N * 4 + uint64_t(n_tiles) * 4;
     static const char* wfn[] = {"w4g128", "w8mul", "w8fpaintb", "w8pass"};

@@ -44,9 +44,9 @@ int schedule_wq_gemv2(int M, int N, int K, bool zp, int sms, G2Sched& s, int mod
         const int rc = schedule_wq_gemv2_cap(M, N, K, zp, sms, s, mode, gcap);
         if(rc == CKB_OK) return (gcap == 99 || s.slot_q >= 1) ? CKB_OK : set_error(CKB_ERR_UNSUPPORTED, "W8 decode kernel: no schedule without empty slots fits in shared memory");
         if(!(mode & 8) || (mode & 1) || s.grid < 1 || s.passes < 1 || s.g_hi < 2) return rc;
-        // measured (profiles/r2_w8_multipass.txt): the multi-pass form beats the stream-K kernel by 10 - 20 % at 14336 x 4096 and loses
-        // 2 - 8 % at 28672 x 8192, where stream-K's ~10 us fixed cost no longer matters: refuse above 128 MiB of weights
-        if((unsigned long long)N * K >= (128ull << 20)) return rc;
+        // measured (profiles/r2_w8_multipass.txt): the multi-pass form beats the stream-K kernel by 10 - 20 % at 14336 x 4096; at
+        // 28672 x 8192 it lost 2 - 8 % to stream-K with two CTAs per SM, and wins by 7 - 8 % now that stream-K runs one CTA per SM
+        // (plan_wq_decode; 64.3 / 76.6 us against 69.2 / 83.3 us at M = 1 / 16, profiles/r2_streamk_two_cta_defect.txt): no size limit
         const int per_cta = (s.n_groups + s.grid - 1) / s.grid;
         gcap = std::min((per_cta + s.passes) / (s.passes + 1), s.g_hi - 1); // groups per slot with one more pass
         if(gcap < 1) return rc;

@@ -102,7 +102,8 @@ def case_w8(M, N, K):
         sc = (torch.rand(N, device="cuda") * 0.01).bfloat16()
         bias = torch.randn(N, device="cuda").bfloat16()
         e = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
-        lst.append(ops.GemmOp(a, b, e, b_op=capi.BOP_MULTIPLY, scale=sc, ds=(bias,), d_strides=((0, 1),), cde_op=capi.CDE_ADD))
+        lst.append(ops.GemmOp(a, b, e, b_op=capi.BOP_MULTIPLY, scale=sc, ds=(bias,), d_strides=((0, 1),), cde_op=capi.CDE_ADD,
+                              flags=int(os.environ.get("PERF_W8_FLAGS", 0))))   # 128 = CKB_FLAG_W8_STREAMK
     us = timeit(lst, 3)
     by = 2 * M * K + N * K + 2 * N * 2 + 2 * M * N
     print(f"w8 mul+bias M{M} N{N} K{K}: {us:.1f} us  {by/us/1e3:.0f} GB/s  {2*M*N*K/us/1e6:.1f} TFLOP/s  kernel={lst[0].kernel_name}")
