@@ -70,7 +70,7 @@ struct G2Args
     EpiParams ep;
 };
 
-static __device__ __noinline__ void g2_store_one(const EpiParams& ep, int m, int n, float acc)
+static __device__ __forceinline__ void g2_store_one_body(const EpiParams& ep, int m, int n, float acc)
 {
     float d0 = 0.f, d1 = 0.f;
     if(ep.num_d > 0) d0 = load_d_f32(ep.d_dtype[0], ep.d[0], (long long)m * ep.d_sm[0] + (long long)n * ep.d_sn[0]);
@@ -80,6 +80,17 @@ static __device__ __noinline__ void g2_store_one(const EpiParams& ep, int m, int
     if(ep.e_dtype == CKB_BF16) static_cast<uint16_t*>(ep.e)[off] = f32_to_bf16_bits(v, ep.flags);
     else if(ep.e_dtype == CKB_F16) static_cast<__half*>(ep.e)[off] = __float2half_rn(v);
     else static_cast<float*>(ep.e)[off] = v;
+}
+// Out of line for the W4 instantiations: the headline path (PassThrough, 16-bit E) never calls it and is 2-5 % slower with the code
+// inlined.  Inlined for the int8-weight instantiations (INL), whose callers usually carry a bias: out of line, `ep` is a generic
+// pointer into the kernel's parameter window and every field read is a cold global-latency load (~0.8 us per launch;
+// W8 + bias decode 4-12 % faster inlined, profiles/r2_w8_store_inline.txt, r2_gemv_red4.txt).
+static __device__ __noinline__ void g2_store_one_call(const EpiParams& ep, int m, int n, float acc) { g2_store_one_body(ep, m, n, acc); }
+template <bool INL>
+static __device__ __forceinline__ void g2_store_one(const EpiParams& ep, int m, int n, float acc)
+{
+    if(INL) g2_store_one_body(ep, m, n, acc);
+    else g2_store_one_call(ep, m, n, acc);
 }
 
 // EXT instantiation only: the same element into this rank's slot of every rank's gathered buffer (fused all-gather, ckb.h)
@@ -486,7 +497,7 @@ wq_gemv2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                         if(EXT && args.num_peers > 0)
                             g2_store_peers(ep, m, n, vv[r], (args.dbg & 32) ? 1 : args.num_peers, (args.dbg & 32) ? &args.e_peer[args.peer_rank] : args.e_peer);
                         else
-                            g2_store_one(ep, m, n, vv[r]);
+                            g2_store_one<WF != 0>(ep, m, n, vv[r]);
                 }
             }
         }
