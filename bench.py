@@ -118,42 +118,54 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
+def workload_config(nl, world):
+    """`config` of the JSON line: the same dict on both arms (--impl ours / reference), so that the driver compares like with like."""
+    return {"workload": f"llama2-7b decode W4A16 g128: M in {{1,4,16}} x {nl} layers x 7 GEMMs "
+                        "((4096,4096)x4,(11008,4096)x2,(4096,11008)x1)",
+            "l2": "inputs larger than L2 (3.4 GB of distinct weights per step)",
+            "parallelism": f"x{world} independent replicas of the GEMM list, one per GPU, own weights, no collective (weak scaling); "
+                           "the N-sharded strong-scaling measurement of one global weight is the cfg5_sharded block"}
+
+
 # --------------------------------------------------------------------------------------------------
 def run_reference(args, rank, world):
-    """--impl reference: the reference's CPU path (the restated ReferenceGemm oracle, all host
-    threads) on a bounded sample of the same workload: one layer's 7 GEMMs at M=4 per step."""
+    """--impl reference: the reference's CPU path (the restated ReferenceGemm oracle, all host threads) on a bounded sample of
+    the same workload and the same `config`: per step ONE layer's 7 GEMMs at every M of the mix (21 GEMMs = 1/32 of the GPU arm's
+    step, same shape and M mix, so the GB/s figures are like for like)."""
     if rank != 0:
         return
     import numpy as np
     from oracle import ck_oracle as orc
     rng = np.random.default_rng(0)
     threads = orc.lib().orc_hardware_threads()
-    M = 4
-    probs = []
+    weights = []
     for (N, K) in LAYER_SHAPES:
-        a = orc.bf16_trunc(rng.standard_normal((M, K)).astype(np.float32))
         q = rng.integers(0, 16, (K, N), dtype=np.uint8)
         s = orc.bf16_trunc((rng.random((K // GROUP, N)) * 0.015 + 0.005).astype(np.float32))
-        probs.append((a, q, s, N, K))
+        weights.append((q, s, N, K))
+    acts = {(M, K): orc.bf16_trunc(rng.standard_normal((M, K)).astype(np.float32)) for M in MS for K in (4096, 11008)}
 
     def step():
-        for a, q, s, N, K in probs:
-            orc.gemm(a, orc.BF16, q, orc.U8, orc.BF16, b_op=orc.BOP_GROUP_F32, scale=s, s_dtype=orc.BF16,
-                     zero_const=8, group_size=GROUP)
+        for M in MS:
+            for q, s, N, K in weights:
+                orc.gemm(acts[(M, K)], orc.BF16, q, orc.U8, orc.BF16, b_op=orc.BOP_GROUP_F32, scale=s, s_dtype=orc.BF16,
+                         zero_const=8, group_size=GROUP)
     for _ in range(min(args.warmup, 1)):
         step()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         step()
     dt = (time.perf_counter() - t0) / args.steps
-    nbytes = sum(algo_bytes(M, N, K) for (N, K) in LAYER_SHAPES)
+    nbytes = sum(algo_bytes(M, N, K) for M in MS for (N, K) in LAYER_SHAPES)
     val = nbytes / dt / 1e9
-    sample = "one layer (7 GEMMs) at M=4 per step = 1/96 of the GPU step's GEMM list"
+    sample = (f"one layer (7 GEMMs) at every M in {{1,4,16}} per step = 21 GEMMs = 1/{args.layers} of the GPU arm's step "
+              "(same shape and M mix; restated ReferenceGemm, ab_scale host pattern, all host threads)")
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": "GB/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": "llama2-7b decode W4A16 g128, M in {1,4,16}, 32 layers x 7 GEMMs", "sample": sample},
+        "config": workload_config(args.layers, world),
+        "launch": "host threads",
         "cpu_baseline": {"value": val, "unit": "GB/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -420,12 +432,8 @@ def main():
             "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": f"llama2-7b decode W4A16 g128: M in {{1,4,16}} x {nl} layers x 7 GEMMs "
-                                   "((4096,4096)x4,(11008,4096)x2,(4096,11008)x1)",
-                       "launch": "cuda-graph replay" if graph is not None else "eager",
-                       "l2": "inputs larger than L2 (3.4 GB of distinct weights per step)",
-                       "parallelism": f"x{world} independent replicas of the GEMM list, one per GPU, own weights, no collective (weak scaling); "
-                                      "the N-sharded strong-scaling measurement of one global weight is the cfg5_sharded block"},
+            "config": workload_config(nl, world),
+            "launch": "cuda-graph replay" if graph is not None else "eager",
             "tflops": world * step_flops / (ms_per_step * 1e-3) / 1e12,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "algorithmic_bytes_per_launch": step_bytes / launches_per_step,
