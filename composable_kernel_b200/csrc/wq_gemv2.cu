@@ -152,7 +152,11 @@ int plan_wq_gemv2(const ckb_gemm_problem& p, ckb_gemm_plan& plan)
     const int sms  = device_info().sm_count > 0 ? device_info().sm_count : 148;
     G2Sched s{};
     const bool w8  = p.b_op != CKB_BOP_GROUP && p.b_op != CKB_BOP_GROUP_RTN;
-    const int mode = ((p.flags & CKB_FLAG_FIXED_K_ORDER) ? 1 : 0) | (p.b_op == CKB_BOP_GROUP_RTN ? 2 : 0) | (p.num_peers > 0 ? 4 : 0) | (w8 ? 8 : 0);
+    // functor epilogue (D tensors, a CDE functor, fp32 E) on the fp32-scale W4 format: served by the instantiation with the epilogue
+    // inlined, which exists for 128-k units only (mode bit 2 asks the schedule for them, as the peer-store epilogue does)
+    const bool functor = !(p.cde_op == CKB_CDE_PASSTHROUGH && (p.e_dtype == CKB_BF16 || p.e_dtype == CKB_F16));
+    const bool epi     = functor && !w8 && p.b_op == CKB_BOP_GROUP && p.num_peers == 0;
+    const int mode = ((p.flags & CKB_FLAG_FIXED_K_ORDER) ? 1 : 0) | (p.b_op == CKB_BOP_GROUP_RTN ? 2 : 0) | ((p.num_peers > 0 || epi) ? 4 : 0) | (w8 ? 8 : 0);
     if(int rc = schedule_wq_gemv2(p.M, p.N, p.K, zp, sms, s, mode)) return rc;
     gp->nt = s.nt; gp->gw = s.gw; gp->passes = s.passes; gp->slot_q = s.slot_q; gp->slot_r = s.slot_r; gp->g_hi = s.g_hi;
     gp->wn_log2 = s.wn_log2; gp->kbu = s.kbu; gp->upw = s.upw; gp->n_chunks = s.n_chunks; gp->ring = s.ring; gp->stage_bytes = s.stage_bytes;
@@ -214,9 +218,9 @@ int plan_wq_gemv2(const ckb_gemm_problem& p, ckb_gemm_plan& plan)
     plan.split_units     = 1;
     plan.workspace_bytes = 0;
     static const char* wfn[] = {"w4g128", "w8mul", "w8fpaintb", "w8pass"};
-    snprintf(plan.kernel_name, sizeof plan.kernel_name, "wq_gemv2_%s%s_%s_hmma_%dx%dwarps_g%d_p%d_m%d_u%dx%d_r%d%s", wfn[gp->wf], (mode & 2) ? "rtn" : "",
+    snprintf(plan.kernel_name, sizeof plan.kernel_name, "wq_gemv2_%s%s_%s_hmma_%dx%dwarps_g%d_p%d_m%d_u%dx%d_r%d%s%s", wfn[gp->wf], (mode & 2) ? "rtn" : "",
              f16 ? "f16" : "bf16", 1 << s.wn_log2, g2_warps(s.nt) >> s.wn_log2, s.gw, s.passes, 8 * s.nt, s.upw, s.kbu, s.ring,
-             (mode & 1) ? "_korder" : "");
+             (mode & 1) ? "_korder" : "", (epi && s.kbu == 2) ? "_epi" : "");
     return CKB_OK;
 }
 
@@ -275,6 +279,10 @@ int run_wq_gemv2(const ckb_gemm_problem& p, const ckb_gemm_plan& plan, cudaStrea
     // (mode bit 2), the inputs-ready hint is honoured when the plan happens to use 128-k units and is ignored otherwise
     a.nodep      = ((p.flags & CKB_FLAG_INPUTS_READY) && gp->kbu == 2 && !gp->rtn) ? 1 : 0;
     a.ext        = (a.nodep || p.num_peers > 0) ? 1 : 0;
+    {
+        const bool functor = !(p.cde_op == CKB_CDE_PASSTHROUGH && (p.e_dtype == CKB_BF16 || p.e_dtype == CKB_F16));
+        a.epi = (functor && gp->wf == 0 && !gp->rtn && gp->kbu == 2 && !a.ext) ? 1 : 0;
+    }
     {
         // programmatic dependent launch pays inside a CUDA graph (PDL edges: the next kernel's prologue and weight prefill
         // overlap this one) but an EAGER launch with the attribute costs ~20 us of host time against ~6 us without

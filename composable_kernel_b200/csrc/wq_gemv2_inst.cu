@@ -38,6 +38,7 @@ int GV_FN(int nt, int gw, int kbu, const G2Plan* gp, const G2Args& a, int grid, 
 #define GV_CASE(NT_, GW_)                                                                                                    \
     if(nt == NT_ && gw == GW_)                                                                                               \
     {                                                                                                                        \
+        if(a.epi) return zp ? launch_gemv2<NT_, GW_, 2, F16, true, false, false, 4>(gp, a, grid, st) : launch_gemv2<NT_, GW_, 2, F16, false, false, false, 4>(gp, a, grid, st); \
         if(a.ext) return zp ? launch_gemv2<NT_, GW_, 2, F16, true, false, true>(gp, a, grid, st) : launch_gemv2<NT_, GW_, 2, F16, false, false, true>(gp, a, grid, st); \
         if(a.rtn) return zp ? launch_gemv2<NT_, GW_, 2, F16, true, true, false>(gp, a, grid, st) : launch_gemv2<NT_, GW_, 2, F16, false, true, false>(gp, a, grid, st); \
         if(kbu == 2) return zp ? launch_gemv2<NT_, GW_, 2, F16, true, false, false>(gp, a, grid, st) : launch_gemv2<NT_, GW_, 2, F16, false, false, false>(gp, a, grid, st); \

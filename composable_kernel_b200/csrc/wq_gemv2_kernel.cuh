@@ -59,6 +59,7 @@ struct G2Args
     const uint16_t* ch_scale; // W8 formats 1, 2: per-channel scale [N] in A's type
     int ext;        // launch the EXT instantiation (peers or nodep requested; 128-k units, fp32-scale numerics)
     int nodep;      // CKB_FLAG_INPUTS_READY (EXT instantiation): do not wait for the previous grid before reading A; wait before exit
+    int epi;        // W4, functor epilogue (D tensors / CDE functor / fp32 E): launch the WF = 4 instantiation, which has g2_store_one inlined
     int rtn;        // CKB_BOP_GROUP_RTN: (q - zp) * s rounded once into A's type before the MMA (RTN kernel instantiation)
     int dbg;        // debug knobs (CKB_GEMV_DBG): 1 = skip the math, 8 = skip the copies and waits
     int peer_rank;  // this rank's index among the peers
@@ -81,10 +82,11 @@ static __device__ __forceinline__ void g2_store_one_body(const EpiParams& ep, in
     else if(ep.e_dtype == CKB_F16) static_cast<__half*>(ep.e)[off] = __float2half_rn(v);
     else static_cast<float*>(ep.e)[off] = v;
 }
-// Out of line for the W4 instantiations: the headline path (PassThrough, 16-bit E) never calls it and is 2-5 % slower with the code
-// inlined.  Inlined for the int8-weight instantiations (INL), whose callers usually carry a bias: out of line, `ep` is a generic
-// pointer into the kernel's parameter window and every field read is a cold global-latency load (~0.8 us per launch;
-// W8 + bias decode 4-12 % faster inlined, profiles/r2_w8_store_inline.txt, r2_gemv_red4.txt).
+// Out of line for the plain W4 instantiations: the headline path (PassThrough, 16-bit E) never calls it and is 2-5 % slower with the
+// code inlined.  Inlined (INL) for the int8-weight instantiations, whose callers usually carry a bias, and for the WF = 4
+// instantiations that serve W4 problems with a functor epilogue: out of line, `ep` is a generic pointer into the kernel's parameter
+// window and every field read is a cold global-latency load (0.8 - 1.7 us per launch; W8 + bias decode 4-12 % faster inlined,
+// profiles/r2_w8_store_inline.txt, r2_gemv_red4.txt; a per-thread local copy of the parameters is slower still, r2_w4_bias_epilogue.txt).
 static __device__ __noinline__ void g2_store_one_call(const EpiParams& ep, int m, int n, float acc) { g2_store_one_body(ep, m, n, acc); }
 template <bool INL>
 static __device__ __forceinline__ void g2_store_one(const EpiParams& ep, int m, int n, float acc)
@@ -133,6 +135,7 @@ wq_gemv2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 const __grid_constant__ CUtensorMap tmZ1, const __grid_constant__ G2Args args)
 {
     constexpr uint32_t MAGIC16 = F16 ? 0x6400u : 0x4300u;
+    constexpr bool W8 = WF >= 1 && WF <= 3; // WF == 4: the W4 format again, with the functor epilogue inlined (G2Args::epi)
     constexpr int NW  = g2_warps(NT);
     constexpr int NCH = GW == 1 && NT == 1 && !RTN ? 2 : 1; // independent HMMA accumulation chains per group
     // M <= 8: the zero point is folded out of the unpack (magic + q goes to the tensor core, 7 instead of 11 instructions per
@@ -184,7 +187,7 @@ wq_gemv2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         const uint32_t bar = full_bar(s);
         const bool hi      = (sg == args.g_hi);
         const int rows     = (CHK + 1) >> 1; // scale rows per stage
-        if(WF != 0)
+        if(W8)
         {
             // int8 weights, K-major in HBM: one box of [CHK k-blocks][16 sg rows][64 B] (per-channel scales are read once per pass)
             ptx::mbar_arrive_expect_tx(bar, CHK * RB * 128u + sg * CHK * 1024u);
@@ -329,7 +332,7 @@ wq_gemv2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 for(int gi = 0; gi < GW; ++gi)
                 {
                     if(GW > 1 && gi == GW - 1 && G < GW) break;
-                    if(WF != 0)
+                    if(W8)
                     {
                         // int8 weights: rows g and g + 8 of the group, 16 bytes = the lane's k slice of the 64-k block (k = 16 t + 4 ks + i,
                         // the same permutation the activation fragments use); dequantised with the reference functor's arithmetic and

@@ -85,8 +85,11 @@ def case_w4(M, N, K):
         # PERF_NODEP=n: every GEMM whose index is not a multiple of n declares its inputs independent of its predecessor
         nd = int(os.environ.get("PERF_NODEP", 0))
         fl = capi.FLAG_INPUTS_READY if nd and (len(lst) % nd) else 0
+        extra = {}
+        if os.environ.get("PERF_W4_BIAS"):   # functor epilogue: E = acc + bias[n]
+            extra = dict(ds=(torch.randn(N, device="cuda").bfloat16(),), d_strides=((0, 1),), cde_op=capi.CDE_ADD)
         lst.append(ops.GemmOp(a, packed, e, flags=fl, b_dtype=capi.I4, b_layout=capi.PREPACKED, b_op=BOP_W4(M), N=N, K=K,
-                              scale=sc, zero_const=8, group_size=128))
+                              scale=sc, zero_const=8, group_size=128, **extra))
     lst = lst * int(os.environ.get("PERF_REPEAT", 1))   # longer graphs for small rotations
     us = timeit(lst, 5)
     by = 2 * M * K + N * K // 2 + (K // 128) * N * 2 + 2 * M * N
