@@ -155,6 +155,33 @@ def test_w4a16_decode_vs_oracle(M, N, K, zp):
     assert bad == 0, f"max err {err}"
 
 
+@pytest.mark.parametrize("M,N,K,zp,cde", [(1, 4096, 4096, False, "add"), (4, 1000, 384, False, "add_gelu"), (16, 4096, 4096, True, "add"),
+                                          (8, 11008, 4096, False, "gelu"), (40, 512, 1024, True, "add")])
+def test_w4a16_decode_functor_epilogue_vs_oracle(M, N, K, zp, cde):
+    """W4A16 decode rows with a CDE functor (bias Add / FastGelu / AddFastGelu, the epilogues of example 60 / client 30): the
+    rotating-producer kernel serves them with its functor-epilogue instantiation (`_epi`), the plain epilogue with the lean one."""
+    from composable_kernel_b200 import capi
+    o = orc()
+    rng = np.random.default_rng(N + K + 7 * M)
+    a = rand_bf16(rng, (M, K))
+    q = rng.integers(0, 16, (K, N)).astype(np.uint8)
+    s = o.bf16_trunc((rng.random((K // 128, N)) * 0.015 + 0.005).astype(np.float32))
+    z = rng.integers(0, 16, (K // 128, N)).astype(np.uint8) if zp else None
+    bias = rand_bf16(rng, (N,))
+    op_dev = {"add": capi.CDE_ADD, "gelu": capi.CDE_FASTGELU, "add_gelu": capi.CDE_ADD_FASTGELU}[cde]
+    op_orc = {"add": o.CDE_ADD, "gelu": o.CDE_FASTGELU, "add_gelu": o.CDE_ADD_FASTGELU}[cde]
+    has_d = "add" in cde
+    got, op = H.run_w4a16(a, q, s, z, ds=(H.to_dev(bias, True),) if has_d else (), d_strides=((0, 1),) if has_d else (), cde_op=op_dev)
+    ref = o.gemm(a, o.BF16, q, o.U8, o.BF16, b_op=o.BOP_GROUP_F32, scale=s, s_dtype=o.BF16, zero=z, zero_const=8, group_size=128,
+                 ds=(np.broadcast_to(bias, (M, N)),) if has_d else (), d_dtypes=(o.BF16,) if has_d else (), cde_op=op_orc)
+    bad, err = H.bf16_close(got, ref, RTOL, ATOL)
+    assert bad == 0, f"{op.kernel_name}: max err {err}"
+    if "wq_gemv2" in op.kernel_name:
+        assert op.kernel_name.endswith("_epi"), op.kernel_name
+        _, plain = H.run_w4a16(a, q, s, z)
+        assert not plain.kernel_name.endswith("_epi"), plain.kernel_name
+
+
 def test_w4a16_linearity_and_zero():
     """Size-independent properties at the BASELINE decode shape: E(0) = 0 and E(2a) = 2 E(a) exactly
     (power-of-two scaling commutes with every rounding on the path)."""

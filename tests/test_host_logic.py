@@ -60,7 +60,7 @@ def sched(M, N, K, zp=0, sms=148, mode=0):
 
 @pytest.mark.parametrize("M", [1, 4, 8, 16, 32])
 @pytest.mark.parametrize("N,K", [(4096, 4096), (11008, 4096), (4096, 11008), (28672, 8192), (3584, 8192), (128, 128), (1000, 384), (16, 64)])
-@pytest.mark.parametrize("mode", [0, 1, 2, 3])
+@pytest.mark.parametrize("mode", [0, 1, 2, 3, 4])
 def test_decode_schedule_covers_the_problem_and_fits_the_sm(M, N, K, mode):
     rc, s = sched(M, N, K, zp=1, mode=mode)
     assert rc == 0
@@ -79,7 +79,7 @@ def test_decode_schedule_covers_the_problem_and_fits_the_sm(M, N, K, mode):
     assert s["off_w"] < s["off_s"] <= s["off_z"] <= s["stage_bytes"]
     if mode & 1:   # CKB_FLAG_FIXED_K_ORDER: the K order may not depend on the shape
         assert (s["wn_log2"], s["upw"], s["kbu"]) == ((1 if s["nt"] == 1 else 0), 1, 2) and s["gw"] >= 2
-    if mode & 2:   # RTN numerics: 128-k units only
+    if mode & 6:   # RTN numerics (2), peer-store or functor epilogue (4): those instantiations exist for 128-k units only
         assert s["kbu"] == 2
 
 
